@@ -1,0 +1,188 @@
+"""Gradient synchronisation over NVLink peer memory: communicator, DDP comm hook, and the
+``average_gradients`` drop-in of train-task.py.
+
+Reference paths replaced
+  * DDP Reducer -> default all-reduce hook -> ncclAllReduce per ~25 MiB bucket
+    (SP/torch/nn/parallel/distributed.py:1255-1284, default_hooks.py:18-54), driven by
+    ``accelerator.prepare`` / ``accelerator.backward`` (train-accelerator.py:189,222) and HF
+    Trainer (train-torchrun.py:127,140);
+  * ``average_gradients(model)`` of train-task.py:65-69: one blocking ``dist.all_reduce`` plus
+    one ``/= size`` kernel per parameter tensor.
+
+The torch.distributed process group stays the control plane (rendezvous, handle exchange,
+barriers); only gradient bytes move through libb2ddp's kernels. Single node, world in
+{1, 2, 4, 8}. No NCCL/gloo fallback for the data path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+
+__all__ = ["P2PComm", "HookState", "p2p_allreduce_hook", "register_p2p_comm_hook",
+           "average_gradients", "exchange_handles", "default_comm"]
+
+_WIRE = {"fp32": _lib.B2_F32, "bf16": _lib.B2_BF16}
+_ALGO = {"auto": _lib.B2_ALGO_AUTO, "one_shot": _lib.B2_ALGO_ONE_SHOT, "two_shot": _lib.B2_ALGO_TWO_SHOT}
+
+
+def exchange_handles(handle: bytes, group: Optional[dist.ProcessGroup] = None) -> list[bytes]:
+    """All-gather one fixed-size opaque handle per rank, in rank order, over the control-plane
+    process group (works on gloo and NCCL)."""
+    world = dist.get_world_size(group)
+    if len(handle) != _lib.B2_IPC_HANDLE_BYTES:
+        raise ValueError(f"handle must be {_lib.B2_IPC_HANDLE_BYTES} bytes, got {len(handle)}")
+    gathered: list = [None] * world
+    dist.all_gather_object(gathered, handle, group=group)
+    if any(not isinstance(h, (bytes, bytearray)) or len(h) != len(handle) for h in gathered):
+        raise RuntimeError("handle exchange returned a malformed entry")
+    return [bytes(h) for h in gathered]
+
+
+class P2PComm:
+    """This rank's end of the symmetric staging buffers. Collective: every rank of ``group``
+    must construct it (and later call ``allreduce_``) in the same order."""
+
+    def __init__(self, group: Optional[dist.ProcessGroup] = None, staging_bytes: Optional[int] = None,
+                 wire: str = "fp32", algo: str = "auto"):
+        if not torch.cuda.is_available():
+            raise RuntimeError("P2PComm needs CUDA devices; there is no CPU path")
+        if dist.is_available() and dist.is_initialized():
+            self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        else:
+            self.rank, self.world = 0, 1
+        if self.world not in (1, 2, 4, 8):
+            raise NotImplementedError(f"P2PComm: world size {self.world} (supported: 1, 2, 4, 8 on one node)")
+        if wire not in _WIRE or algo not in _ALGO:
+            raise ValueError(f"wire must be one of {list(_WIRE)}, algo one of {list(_ALGO)}")
+        self.group, self.wire, self.algo = group, wire, algo
+        self.device = torch.device("cuda", torch.cuda.current_device())
+        if staging_bytes is None:
+            staging_bytes = int(os.environ.get("B2_AR_STAGING_MB", "64")) << 20
+        self._lib = _lib.load()
+        self._ctx = C.c_void_p()
+        _lib.check(self._lib.b2_comm_create(self.rank, self.world, staging_bytes, C.byref(self._ctx)))
+        if self.world > 1:
+            raw = C.create_string_buffer(_lib.B2_IPC_HANDLE_BYTES)
+            _lib.check(self._lib.b2_comm_get_handle(self._ctx, raw))
+            handles = exchange_handles(raw.raw, group)
+            _lib.check(self._lib.b2_comm_open_peers(self._ctx, b"".join(handles)))
+            dist.barrier(group)  # every rank has mapped every peer before the first kernel
+
+    def allreduce_(self, tensor: torch.Tensor, scale: float = 1.0, *, wire: Optional[str] = None,
+                   algo: Optional[str] = None, stream: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
+        """In place: tensor <- scale * sum over ranks (fixed rank order; identical on all ranks)."""
+        if self._ctx is None:
+            raise RuntimeError("P2PComm is closed")
+        if tensor.device != self.device:
+            raise RuntimeError(f"tensor on {tensor.device}, communicator on {self.device}")
+        if tensor.dtype != torch.float32:
+            raise NotImplementedError(f"P2PComm.allreduce_: fp32 buckets only (got {tensor.dtype})")
+        if not tensor.is_contiguous():
+            raise ValueError("P2PComm.allreduce_: tensor must be contiguous")
+        s = (stream or torch.cuda.current_stream(self.device)).cuda_stream
+        _lib.check(self._lib.b2_allreduce(self._ctx, tensor.data_ptr(), tensor.numel(),
+                                          _WIRE[wire or self.wire], float(scale),
+                                          _ALGO[algo or self.algo], s))
+        cap = self._lib.b2_comm_max_numel(self._ctx, _WIRE[wire or self.wire])
+        _lib.count_launch(max(1, -(-tensor.numel() // max(cap, 1))))
+        return tensor
+
+    def check(self) -> None:
+        """Synchronising health check: raises if a kernel timed out waiting for a peer."""
+        _lib.check(self._lib.b2_comm_status(self._ctx))
+
+    def close(self) -> None:
+        if self._ctx is not None:
+            torch.cuda.synchronize(self.device)
+            if self.world > 1 and dist.is_initialized():
+                dist.barrier(self.group)  # nobody unmaps while a peer may still read
+            self._lib.b2_comm_destroy(self._ctx)
+            self._ctx = None
+
+    def __del__(self):  # best effort; explicit close() is the collective-safe way
+        try:
+            if getattr(self, "_ctx", None) is not None:
+                self._lib.b2_comm_destroy(self._ctx)
+                self._ctx = None
+        except Exception:
+            pass
+
+
+_default: Optional[P2PComm] = None
+
+
+def default_comm(**kwargs) -> P2PComm:
+    """Process-wide communicator on the default process group (created collectively on first use)."""
+    global _default
+    if _default is None:
+        _default = P2PComm(**kwargs)
+    return _default
+
+
+class HookState:
+    """State object handed to ``ddp.register_comm_hook``: the communicator plus the side stream
+    the reductions run on, so they overlap the rest of backward like the Reducer's NCCL stream."""
+
+    def __init__(self, comm: Optional[P2PComm] = None, **comm_kwargs):
+        self.comm = comm or default_comm(**comm_kwargs)
+        self.stream = torch.cuda.Stream(device=self.comm.device)
+        self.buckets_reduced = 0
+
+
+def p2p_allreduce_hook(state: HookState, bucket: dist.GradBucket) -> torch.futures.Future[torch.Tensor]:
+    """DDP communication hook: mean-all-reduce ``bucket.buffer()`` in place.
+
+    Same result contract as ``default_hooks.allreduce_hook`` (divide by world size, then sum;
+    SP/torch/distributed/algorithms/ddp_comm_hooks/default_hooks.py:18-54). Called by the
+    Reducer on the autograd thread once per ready bucket; the returned future is completed
+    with the side stream current, so ``Reducer::finalize_backward`` orders its copy-out after
+    the kernel without any host synchronisation.
+    """
+    comm = state.comm
+    buf = bucket.buffer()
+    producer = torch.cuda.current_stream(comm.device)
+    state.stream.wait_stream(producer)
+    with torch.cuda.stream(state.stream):
+        comm.allreduce_(buf, 1.0 / comm.world, stream=state.stream)
+        buf.record_stream(state.stream)
+        fut: torch.futures.Future[torch.Tensor] = torch.futures.Future(devices=[comm.device])
+        fut.set_result(buf)
+    state.buckets_reduced += 1
+    return fut
+
+
+def register_p2p_comm_hook(ddp_model, state: Optional[HookState] = None, **comm_kwargs) -> HookState:
+    """``ddp_model.register_comm_hook(state, p2p_allreduce_hook)``; collective on first use."""
+    state = state or HookState(**comm_kwargs)
+    ddp_model.register_comm_hook(state, p2p_allreduce_hook)
+    return state
+
+
+@torch.no_grad()
+def average_gradients(model: torch.nn.Module, comm: Optional[P2PComm] = None) -> None:
+    """Drop-in for train-task.py:65-69 (same signature, same in-place effect on ``p.grad``).
+
+    The reference issues one blocking NCCL all-reduce and one division kernel per parameter
+    tensor (131-557 of each per step). Here all gradients go through ONE flat exchange:
+    pack -> fused scale + all-reduce -> unpack, stream-ordered with the backward that produced
+    the gradients and with the ``optimizer.step()`` that follows at train-task.py:295.
+    """
+    comm = comm or default_comm()
+    grads = [p.grad for p in model.parameters()]  # the reference dereferences every .grad too
+    if any(g is None for g in grads):
+        raise AttributeError("average_gradients: a parameter has no .grad (train-task.py:68 would fail too)")
+    if not grads:
+        return
+    if any(g.dtype != torch.float32 for g in grads):
+        raise NotImplementedError("average_gradients: fp32 gradients only")
+    flat = torch.cat([g.reshape(-1) for g in grads])
+    comm.allreduce_(flat, 1.0 / comm.world)
+    torch._foreach_copy_([g.view(-1) if g.is_contiguous() else g for g in grads],
+                         [c.view_as(g) if not g.is_contiguous() else c
+                          for c, g in zip(flat.split([g.numel() for g in grads]), grads)])

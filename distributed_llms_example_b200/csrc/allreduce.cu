@@ -1,0 +1,530 @@
+// Gradient mean all-reduce over NVLink peer memory (include/b2ddp.h, section (a)).
+//
+// Replaces ncclAllReduce as driven by the DDP Reducer (SP/torch/nn/parallel/distributed.py
+// :1255-1284 -> default_comm_hooks.hpp:36-51; reference call sites train-accelerator.py:189,222
+// and train-torchrun.py:127,140) and by train-task.py:65-69 (per-tensor all_reduce + "/= size").
+//
+// One process per GPU. Every rank owns a "symmetric" allocation [flag pad | staging half 0 |
+// staging half 1] that all peers map through CUDA IPC; NVSwitch gives each GPU full bandwidth
+// to every peer, so there is no ring: every CTA talks to all peers at once.
+//
+//   one kernel per call:
+//     copy-in   bucket (ordinary caching-allocator memory) -> own staging, fused with the
+//               1/world scale and the optional fp32->bf16 wire cast
+//     barrier   per-CTA flags in peer memory (st.release.sys / ld.acquire.sys)
+//     one-shot  every rank pulls all W staged copies, adds them in rank order 0..W-1 in fp32
+//               and writes the bucket                     (latency-optimal, (W-1)*S inbound)
+//     two-shot  rank r reduces slice r the same way, publishes it in its own staging,
+//               barrier, every rank pulls the other W-1 reduced slices
+//                                                  (bandwidth-optimal, 2(W-1)/W*S inbound)
+//
+// Fixed rank-order summation makes the result bit-identical on every rank for both
+// algorithms. Consecutive calls alternate staging halves, which is what makes a trailing
+// barrier unnecessary: a rank can only be two calls ahead of a peer's reads if it passed
+// the barrier of the call in between, which that peer enters only after finishing its reads.
+// Calls on one b2_comm must therefore be stream-ordered on every rank.
+#include <cstdlib>
+#include <cstring>
+
+#include "common.cuh"
+
+namespace b2 {
+
+constexpr int kArThreads = 512;
+constexpr int kArMaxBlocks = 128;                                        // rows of the flag pad
+constexpr size_t kPadBytes = 16384;                                      // flags + status word
+constexpr size_t kStatusOff = kArMaxBlocks * B2_MAX_WORLD * 4;           // after the flags
+static_assert(kStatusOff + 64 <= kPadBytes, "flag pad too small");
+
+struct RankView {
+  float* buf;                        // this rank's bucket, reduced in place
+  char* stage[B2_MAX_WORLD];         // staging half of every rank, as mapped by this rank
+  uint32_t* flags[B2_MAX_WORLD];     // flag pad of every rank, as mapped by this rank
+  uint32_t* status;                  // this rank's sticky timeout word
+  int rank;
+};
+
+template <int NV>
+struct ArArgs {
+  RankView v[NV];
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+// Peer (or own) staging written by another GPU during this kernel: relaxed system-scope load,
+// never the non-coherent path.
+__device__ __forceinline__ uint4 ld_peer16(const void* p) {
+  uint4 r;
+  asm volatile("ld.relaxed.sys.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p)
+               : "memory");
+  return r;
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+// All CTAs with the same blockIdx.x on all ranks meet here. Data written by any thread of
+// the CTA before the call is visible to the peers' CTAs after it (bar.sync orders the CTA's
+// writes before the releasing store; the peer's acquiring load orders its reads after).
+template <int W>
+__device__ __forceinline__ void cross_barrier(const RankView& v, uint32_t epoch,
+                                              unsigned long long timeout_ns) {
+  __syncthreads();
+  if (W > 1 && threadIdx.x < W) {
+    const int peer = threadIdx.x;
+    st_release_sys(v.flags[peer] + blockIdx.x * B2_MAX_WORLD + v.rank, epoch);
+    const uint32_t* mine = v.flags[v.rank] + blockIdx.x * B2_MAX_WORLD + peer;
+    const unsigned long long t0 = globaltimer_ns();
+    unsigned spins = 0;
+    while ((int)(ld_acquire_sys(mine) - epoch) < 0) {
+      if ((++spins & 1023u) == 0 && globaltimer_ns() - t0 > timeout_ns) {
+        atomicExch(v.status, 1u);  // sticky; b2_comm_status reports B2_ERR_TIMEOUT
+        break;
+      }
+    }
+  }
+  __syncthreads();
+}
+
+template <bool BF16W>
+struct Wire;
+template <>
+struct Wire<false> {
+  static constexpr int kElems = 4;  // elements per 16-byte staged pack
+  static __device__ __forceinline__ uint4 load_scaled(const float* buf, long long pack, float scale) {
+    uint4 u = ld_stream16(buf + pack * 4);
+    u.x = __float_as_uint(__fmul_rn(__uint_as_float(u.x), scale));
+    u.y = __float_as_uint(__fmul_rn(__uint_as_float(u.y), scale));
+    u.z = __float_as_uint(__fmul_rn(__uint_as_float(u.z), scale));
+    u.w = __float_as_uint(__fmul_rn(__uint_as_float(u.w), scale));
+    return u;
+  }
+  static __device__ __forceinline__ void to_f(uint4 u, float* x) {
+    x[0] = __uint_as_float(u.x); x[1] = __uint_as_float(u.y);
+    x[2] = __uint_as_float(u.z); x[3] = __uint_as_float(u.w);
+  }
+  static __device__ __forceinline__ uint4 from_f(const float* x) {
+    return make_uint4(__float_as_uint(x[0]), __float_as_uint(x[1]), __float_as_uint(x[2]),
+                      __float_as_uint(x[3]));
+  }
+  static __device__ __forceinline__ void store_buf(float* buf, long long pack, uint4 staged) {
+    *reinterpret_cast<uint4*>(buf + pack * 4) = staged;
+  }
+  static __device__ __forceinline__ float stage1(const float* buf, long long e, float scale) {
+    return __fmul_rn(buf[e], scale);
+  }
+  // tail elements (numel % kElems) live after the last whole pack of the staging half
+  static __device__ __forceinline__ void tail_store(char* base, int i, float f) {
+    reinterpret_cast<float*>(base)[i] = f;
+  }
+  static __device__ __forceinline__ float tail_load(const char* base, int i) {
+    return reinterpret_cast<const volatile float*>(base)[i];
+  }
+  static __device__ __forceinline__ float round_wire(float f) { return f; }
+};
+template <>
+struct Wire<true> {
+  static constexpr int kElems = 8;
+  static __device__ __forceinline__ uint4 load_scaled(const float* buf, long long pack, float scale) {
+    const uint4 a = ld_stream16(buf + pack * 8), b = ld_stream16(buf + pack * 8 + 4);
+    return make_uint4(
+        pack_bf16(__uint_as_float(a.x) * scale, __uint_as_float(a.y) * scale),
+        pack_bf16(__uint_as_float(a.z) * scale, __uint_as_float(a.w) * scale),
+        pack_bf16(__uint_as_float(b.x) * scale, __uint_as_float(b.y) * scale),
+        pack_bf16(__uint_as_float(b.z) * scale, __uint_as_float(b.w) * scale));
+  }
+  static __device__ __forceinline__ void to_f(uint4 u, float* x) {
+    x[0] = bf16lo(u.x); x[1] = bf16hi(u.x); x[2] = bf16lo(u.y); x[3] = bf16hi(u.y);
+    x[4] = bf16lo(u.z); x[5] = bf16hi(u.z); x[6] = bf16lo(u.w); x[7] = bf16hi(u.w);
+  }
+  static __device__ __forceinline__ uint4 from_f(const float* x) {
+    return make_uint4(pack_bf16(x[0], x[1]), pack_bf16(x[2], x[3]), pack_bf16(x[4], x[5]),
+                      pack_bf16(x[6], x[7]));
+  }
+  static __device__ __forceinline__ void store_buf(float* buf, long long pack, uint4 staged) {
+    float x[8];
+    to_f(staged, x);
+    uint4* o = reinterpret_cast<uint4*>(buf + pack * 8);
+    o[0] = make_uint4(__float_as_uint(x[0]), __float_as_uint(x[1]), __float_as_uint(x[2]), __float_as_uint(x[3]));
+    o[1] = make_uint4(__float_as_uint(x[4]), __float_as_uint(x[5]), __float_as_uint(x[6]), __float_as_uint(x[7]));
+  }
+  static __device__ __forceinline__ float stage1(const float* buf, long long e, float scale) {
+    return round_wire(buf[e] * scale);
+  }
+  static __device__ __forceinline__ void tail_store(char* base, int i, float f) {
+    reinterpret_cast<unsigned short*>(base)[i] = (unsigned short)(__float_as_uint(round_wire(f)) >> 16);
+  }
+  static __device__ __forceinline__ float tail_load(const char* base, int i) {
+    return __uint_as_float((uint32_t) reinterpret_cast<const volatile unsigned short*>(base)[i] << 16);
+  }
+  static __device__ __forceinline__ float round_wire(float f) {
+    return __bfloat162float(__float2bfloat16_rn(f));
+  }
+};
+
+// Sum of pack `i` over all ranks, rank order 0..W-1, fp32 adds (no fma, no reassociation).
+template <int W, bool BF16W>
+__device__ __forceinline__ void reduce_packs(const RankView& v, long long i, float* acc) {
+  using Wr = Wire<BF16W>;
+  uint4 r[W];
+#pragma unroll
+  for (int k = 0; k < W; ++k) r[k] = ld_peer16(v.stage[k] + i * 16);
+  Wr::to_f(r[0], acc);
+#pragma unroll
+  for (int k = 1; k < W; ++k) {
+    float x[Wr::kElems];
+    Wr::to_f(r[k], x);
+#pragma unroll
+    for (int e = 0; e < Wr::kElems; ++e) acc[e] = __fadd_rn(acc[e], x[e]);
+  }
+}
+
+template <int W, bool BF16W, int ALGO, int NV>
+__global__ void __launch_bounds__(kArThreads, 1)
+allreduce_kernel(const __grid_constant__ ArArgs<NV> args, long long numel, float scale,
+                 uint32_t epoch, unsigned long long timeout_ns) {
+  using Wr = Wire<BF16W>;
+  constexpr int EPP = Wr::kElems;
+  const RankView& v = args.v[NV == 1 ? 0 : blockIdx.y];
+  const int rank = v.rank;
+  const int nb = gridDim.x, b = blockIdx.x, tid = threadIdx.x;
+  const long long npack = numel / EPP;
+  float* __restrict__ buf = v.buf;
+  char* own = v.stage[rank];
+  // Elements past the last whole pack ride in block 0, one-shot style, for both algorithms.
+  const long long tail0 = npack * EPP;
+  char* own_tail = own + npack * 16;
+
+  if (ALGO == B2_ALGO_ONE_SHOT || W == 1) {
+    const long long c = (npack + nb - 1) / nb;
+    const long long lo = min((long long)b * c, npack), hi = min(lo + c, npack);
+    for (long long i = lo + tid; i < hi; i += kArThreads)
+      *reinterpret_cast<uint4*>(own + i * 16) = Wr::load_scaled(buf, i, scale);
+    if (b == 0 && tid < numel - tail0) Wr::tail_store(own_tail, tid, Wr::stage1(buf, tail0 + tid, scale));
+    cross_barrier<W>(v, epoch, timeout_ns);
+    constexpr int U = (W >= 8) ? 2 : 4;
+    long long i = lo + tid;
+    for (; i + (U - 1) * kArThreads < hi; i += U * kArThreads) {
+      float acc[U][EPP];
+#pragma unroll
+      for (int u = 0; u < U; ++u) reduce_packs<W, BF16W>(v, i + u * kArThreads, acc[u]);
+#pragma unroll
+      for (int u = 0; u < U; ++u) Wr::store_buf(buf, i + u * kArThreads, Wr::from_f(acc[u]));
+    }
+    for (; i < hi; i += kArThreads) {
+      float acc[EPP];
+      reduce_packs<W, BF16W>(v, i, acc);
+      Wr::store_buf(buf, i, Wr::from_f(acc));
+    }
+  } else {
+    const long long Q = (npack + W - 1) / W;   // packs per rank slice
+    const long long q = (Q + nb - 1) / nb;     // packs per (slice, block) sub-range
+    // copy-in: this CTA stages its sub-range of EVERY slice, because the peer CTA with the
+    // same blockIdx is the one that will read it after the per-CTA barrier.
+#pragma unroll 1
+    for (int s = 0; s < W; ++s) {
+      const long long slo = min((long long)s * Q, npack), shi = min(slo + Q, npack);
+      const long long lo = min(slo + (long long)b * q, shi), hi = min(lo + q, shi);
+      for (long long i = lo + tid; i < hi; i += kArThreads)
+        *reinterpret_cast<uint4*>(own + i * 16) = Wr::load_scaled(buf, i, scale);
+    }
+    if (b == 0 && tid < numel - tail0) Wr::tail_store(own_tail, tid, Wr::stage1(buf, tail0 + tid, scale));
+    cross_barrier<W>(v, epoch, timeout_ns);
+    // reduce-scatter: my slice, my sub-range, summed over all ranks; publish in place.
+    {
+      const long long slo = min((long long)rank * Q, npack), shi = min(slo + Q, npack);
+      const long long lo = min(slo + (long long)b * q, shi), hi = min(lo + q, shi);
+      constexpr int U = (W >= 8) ? 2 : 4;
+      long long i = lo + tid;
+      for (; i + (U - 1) * kArThreads < hi; i += U * kArThreads) {
+        float acc[U][EPP];
+#pragma unroll
+        for (int u = 0; u < U; ++u) reduce_packs<W, BF16W>(v, i + u * kArThreads, acc[u]);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const uint4 o = Wr::from_f(acc[u]);
+          *reinterpret_cast<uint4*>(own + (i + u * kArThreads) * 16) = o;
+          Wr::store_buf(buf, i + u * kArThreads, o);
+        }
+      }
+      for (; i < hi; i += kArThreads) {
+        float acc[EPP];
+        reduce_packs<W, BF16W>(v, i, acc);
+        const uint4 o = Wr::from_f(acc);
+        *reinterpret_cast<uint4*>(own + i * 16) = o;
+        Wr::store_buf(buf, i, o);
+      }
+    }
+    cross_barrier<W>(v, epoch + 1, timeout_ns);
+    // all-gather: pull the other ranks' reduced sub-ranges, starting with my right-hand
+    // neighbour so that the W ranks do not all hit the same peer at the same time.
+    constexpr int U2 = 4;
+#pragma unroll 1
+    for (int k = 1; k < W; ++k) {
+      const int s = (rank + k) % W;
+      const char* src = v.stage[s];
+      const long long slo = min((long long)s * Q, npack), shi = min(slo + Q, npack);
+      const long long lo = min(slo + (long long)b * q, shi), hi = min(lo + q, shi);
+      long long i = lo + tid;
+      for (; i + (U2 - 1) * kArThreads < hi; i += U2 * kArThreads) {
+        uint4 r[U2];
+#pragma unroll
+        for (int u = 0; u < U2; ++u) r[u] = ld_peer16(src + (i + u * kArThreads) * 16);
+#pragma unroll
+        for (int u = 0; u < U2; ++u) Wr::store_buf(buf, i + u * kArThreads, r[u]);
+      }
+      for (; i < hi; i += kArThreads) Wr::store_buf(buf, i, ld_peer16(src + i * 16));
+    }
+  }
+  // tail elements (fewer than one pack): every rank sums them itself after the first barrier
+  if (b == 0 && tid < numel - tail0) {
+    float acc = 0.f;
+#pragma unroll
+    for (int k = 0; k < W; ++k) {
+      const float x = Wr::tail_load(v.stage[k] + npack * 16, tid);
+      acc = (k == 0) ? x : __fadd_rn(acc, x);
+    }
+    buf[tail0 + tid] = Wr::round_wire(acc);
+  }
+}
+
+// ---- host side ----------------------------------------------------------------------
+
+using KernelFn = const void*;
+
+template <int NV>
+static KernelFn pick_kernel(int world, bool bf16w, int algo) {
+#define B2_AR_CASE(Wv)                                                                        \
+  if (world == Wv) {                                                                          \
+    if (algo == B2_ALGO_ONE_SHOT)                                                             \
+      return bf16w ? (KernelFn)allreduce_kernel<Wv, true, B2_ALGO_ONE_SHOT, NV>               \
+                   : (KernelFn)allreduce_kernel<Wv, false, B2_ALGO_ONE_SHOT, NV>;             \
+    return bf16w ? (KernelFn)allreduce_kernel<Wv, true, B2_ALGO_TWO_SHOT, NV>                 \
+                 : (KernelFn)allreduce_kernel<Wv, false, B2_ALGO_TWO_SHOT, NV>;               \
+  }
+  B2_AR_CASE(1)
+  B2_AR_CASE(2)
+  B2_AR_CASE(4)
+  B2_AR_CASE(8)
+#undef B2_AR_CASE
+  return nullptr;
+}
+
+static long long env_ll(const char* name, long long dflt) {
+  const char* s = std::getenv(name);
+  if (!s || !*s) return dflt;
+  char* end = nullptr;
+  long long v = std::strtoll(s, &end, 10);
+  return (end && *end == 0) ? v : dflt;
+}
+
+// One-shot moves (W-1)*S inbound per rank and needs one barrier; two-shot moves
+// 2(W-1)/W*S and needs two. At W=2 the bytes are equal, so one-shot always wins.
+static int pick_algo(int world, long long bytes) {
+  if (world <= 2) return B2_ALGO_ONE_SHOT;
+  const long long thresh = env_ll("B2_AR_ONE_SHOT_MAX_BYTES", world == 4 ? (1ll << 20) : (512ll << 10));
+  return bytes <= thresh ? B2_ALGO_ONE_SHOT : B2_ALGO_TWO_SHOT;
+}
+
+static int pick_blocks(long long npack, int max_blocks) {
+  // ~2 packs-of-4-unroll per thread before adding a CTA; small buckets stay on few CTAs so
+  // the barrier is cheap and the backward GEMMs keep their SMs.
+  long long nb = (npack + (long long)kArThreads * 8 - 1) / ((long long)kArThreads * 8);
+  if (nb < 1) nb = 1;
+  if (nb > max_blocks) nb = max_blocks;
+  return (int)nb;
+}
+
+}  // namespace b2
+
+struct b2_comm {
+  int rank = 0, world = 1, device = 0;
+  size_t half_bytes = 0;
+  char* base[B2_MAX_WORLD] = {nullptr};  // mapped symmetric allocation of every rank
+  bool opened = false;
+  uint32_t epoch = 1;
+  int parity = 0;
+  int max_blocks = 64;
+  unsigned long long timeout_ns = 30ull * 1000000000ull;
+};
+
+extern "C" int b2_comm_create(int rank, int world, size_t staging_bytes, b2_comm** out) {
+  using namespace b2;
+  B2_REQUIRE(out, "comm_create: null out");
+  B2_REQUIRE(world == 1 || world == 2 || world == 4 || world == 8,
+             "comm_create: world %d not in {1,2,4,8}", world);
+  B2_REQUIRE(rank >= 0 && rank < world, "comm_create: rank %d outside [0,%d)", rank, world);
+  B2_REQUIRE(staging_bytes >= 4096, "comm_create: staging_bytes %zu < 4096", staging_bytes);
+  b2_comm* c = new b2_comm();
+  c->rank = rank;
+  c->world = world;
+  c->half_bytes = (staging_bytes + 255) & ~(size_t)255;
+  c->max_blocks = (int)env_ll("B2_AR_BLOCKS", 64);
+  if (c->max_blocks < 1) c->max_blocks = 1;
+  if (c->max_blocks > kArMaxBlocks) c->max_blocks = kArMaxBlocks;
+  c->timeout_ns = (unsigned long long)env_ll("B2_AR_TIMEOUT_MS", 30000) * 1000000ull;
+  cudaError_t e = cudaGetDevice(&c->device);
+  if (e == cudaSuccess) e = cudaMalloc((void**)&c->base[rank], kPadBytes + 2 * c->half_bytes);
+  if (e == cudaSuccess) e = cudaMemset(c->base[rank], 0, kPadBytes);
+  if (e != cudaSuccess) {
+    delete c;
+    return fail(B2_ERR_CUDA, "comm_create: %s", cudaGetErrorString(e));
+  }
+  c->opened = (world == 1);
+  *out = c;
+  return B2_OK;
+}
+
+extern "C" int b2_comm_get_handle(b2_comm* c, void* handle_out) {
+  using namespace b2;
+  B2_REQUIRE(c && handle_out, "comm_get_handle: null pointer");
+  static_assert(sizeof(cudaIpcMemHandle_t) == B2_IPC_HANDLE_BYTES, "IPC handle size");
+  cudaIpcMemHandle_t h;
+  B2_CUDA_CHECK(cudaIpcGetMemHandle(&h, c->base[c->rank]));
+  std::memcpy(handle_out, &h, sizeof(h));
+  return B2_OK;
+}
+
+extern "C" int b2_comm_open_peers(b2_comm* c, const void* handles) {
+  using namespace b2;
+  B2_REQUIRE(c && handles, "comm_open_peers: null pointer");
+  if (c->opened) return B2_OK;
+  for (int r = 0; r < c->world; ++r) {
+    if (r == c->rank) continue;
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, (const char*)handles + (size_t)r * B2_IPC_HANDLE_BYTES, sizeof(h));
+    B2_CUDA_CHECK(cudaIpcOpenMemHandle((void**)&c->base[r], h, cudaIpcMemLazyEnablePeerAccess));
+  }
+  c->opened = true;
+  return B2_OK;
+}
+
+extern "C" int64_t b2_comm_max_numel(b2_comm* c, int wire_dtype) {
+  if (!c) return b2::fail(B2_ERR_INVALID, "comm_max_numel: null comm");
+  const size_t elt = wire_dtype == B2_BF16 ? 2 : 4;
+  return (int64_t)((c->half_bytes - 64) / elt);
+}
+
+extern "C" int b2_allreduce(b2_comm* c, void* buf, int64_t numel, int wire_dtype, float scale,
+                            int algo, b2_stream_t stream) {
+  using namespace b2;
+  B2_REQUIRE(c, "allreduce: null comm");
+  if (!c->opened) return fail(B2_ERR_STATE, "allreduce: b2_comm_open_peers has not been called");
+  B2_REQUIRE(wire_dtype == B2_F32 || wire_dtype == B2_BF16, "allreduce: wire dtype %d", wire_dtype);
+  B2_REQUIRE(algo >= B2_ALGO_AUTO && algo <= B2_ALGO_TWO_SHOT, "allreduce: algo %d", algo);
+  B2_REQUIRE(numel >= 0, "allreduce: negative numel");
+  if (numel == 0) return B2_OK;
+  B2_REQUIRE(buf, "allreduce: null buffer");
+  B2_REQUIRE((((uintptr_t)buf) & 15) == 0, "allreduce: buffer must be 16-byte aligned");
+  const bool bf16w = wire_dtype == B2_BF16;
+  const int epp = bf16w ? 8 : 4;
+  // elements per launch: whole packs, so that every chunk start stays 16-byte aligned
+  const long long cap = (b2_comm_max_numel(c, wire_dtype) / epp) * epp;
+  for (long long off = 0; off < numel; off += cap) {
+    const long long n = (numel - off < cap) ? (numel - off) : cap;
+    const int a = algo == B2_ALGO_AUTO ? pick_algo(c->world, n * 4) : algo;
+    ArArgs<1> args;
+    RankView& v = args.v[0];
+    v.buf = (float*)buf + off;
+    v.rank = c->rank;
+    for (int r = 0; r < B2_MAX_WORLD; ++r) {
+      char* base = c->base[r < c->world ? r : c->rank];
+      v.stage[r] = base + kPadBytes + (size_t)c->parity * c->half_bytes;
+      v.flags[r] = (uint32_t*)base;
+    }
+    v.status = (uint32_t*)(c->base[c->rank] + kStatusOff);
+    KernelFn fn = pick_kernel<1>(c->world, bf16w, a);
+    if (!fn) return fail(B2_ERR_INVALID, "allreduce: no kernel for world %d", c->world);
+    const int nb = pick_blocks(n / epp, c->max_blocks);
+    long long n_arg = n;
+    float scale_arg = scale;
+    uint32_t epoch = c->epoch;
+    unsigned long long to = c->timeout_ns;
+    void* kargs[] = {&args, &n_arg, &scale_arg, &epoch, &to};
+    B2_CUDA_CHECK(cudaLaunchKernel(fn, dim3(nb), dim3(kArThreads), kargs, 0, (cudaStream_t)stream));
+    c->epoch += 2;
+    c->parity ^= 1;
+  }
+  return B2_OK;
+}
+
+extern "C" int b2_comm_status(b2_comm* c) {
+  using namespace b2;
+  B2_REQUIRE(c, "comm_status: null comm");
+  uint32_t s = 0;
+  B2_CUDA_CHECK(cudaMemcpy(&s, c->base[c->rank] + kStatusOff, 4, cudaMemcpyDeviceToHost));
+  if (s != 0) return fail(B2_ERR_TIMEOUT, "allreduce: a peer did not reach a barrier within %llu ms",
+                          c->timeout_ns / 1000000ull);
+  return B2_OK;
+}
+
+extern "C" int b2_comm_destroy(b2_comm* c) {
+  using namespace b2;
+  if (!c) return B2_OK;
+  for (int r = 0; r < c->world; ++r) {
+    if (!c->base[r]) continue;
+    if (r == c->rank) cudaFree(c->base[r]); else cudaIpcCloseMemHandle(c->base[r]);
+  }
+  delete c;
+  return B2_OK;
+}
+
+extern "C" size_t b2_allreduce_emulated_scratch_bytes(int world, int64_t numel) {
+  if (world < 1 || numel < 0) return 0;
+  const size_t half = (((size_t)numel * 4 + 64) + 255) & ~(size_t)255;
+  return (size_t)world * (b2::kPadBytes + half);
+}
+
+extern "C" int b2_allreduce_emulated(void* const* bufs_host, int world, int64_t numel,
+                                     int wire_dtype, float scale, int algo, void* staging,
+                                     b2_stream_t stream) {
+  using namespace b2;
+  B2_REQUIRE(bufs_host && staging, "allreduce_emulated: null pointer");
+  B2_REQUIRE(world == 1 || world == 2 || world == 4 || world == 8, "allreduce_emulated: world %d", world);
+  B2_REQUIRE(algo == B2_ALGO_ONE_SHOT || algo == B2_ALGO_TWO_SHOT, "allreduce_emulated: algo %d", algo);
+  B2_REQUIRE(wire_dtype == B2_F32 || wire_dtype == B2_BF16, "allreduce_emulated: wire dtype");
+  B2_REQUIRE(numel > 0, "allreduce_emulated: numel must be positive");
+  const bool bf16w = wire_dtype == B2_BF16;
+  const int epp = bf16w ? 8 : 4;
+  const size_t half = (((size_t)numel * 4 + 64) + 255) & ~(size_t)255;
+  const size_t per_rank = kPadBytes + half;
+  cudaStream_t st = (cudaStream_t)stream;
+  for (int r = 0; r < world; ++r)
+    B2_CUDA_CHECK(cudaMemsetAsync((char*)staging + r * per_rank, 0, kPadBytes, st));
+  ArArgs<B2_MAX_WORLD> args;
+  for (int r = 0; r < B2_MAX_WORLD; ++r) {
+    RankView& v = args.v[r];
+    const int me = r < world ? r : 0;
+    B2_REQUIRE(bufs_host[me] && (((uintptr_t)bufs_host[me]) & 15) == 0,
+               "allreduce_emulated: buffer %d null or not 16-byte aligned", me);
+    v.buf = (float*)bufs_host[me];
+    v.rank = me;
+    for (int k = 0; k < B2_MAX_WORLD; ++k) {
+      char* base = (char*)staging + (size_t)(k < world ? k : me) * per_rank;
+      v.stage[k] = base + kPadBytes;
+      v.flags[k] = (uint32_t*)base;
+    }
+    v.status = (uint32_t*)((char*)staging + (size_t)me * per_rank + kStatusOff);
+  }
+  KernelFn fn = pick_kernel<B2_MAX_WORLD>(world, bf16w, algo);
+  // The virtual ranks' CTAs wait on one another, so they must all be resident: cooperative
+  // launch, and few enough CTAs (<= 1 per SM with 512 threads is always resident on 148 SMs).
+  int nb = pick_blocks(numel / epp, 16);
+  long long n_arg = numel;
+  float scale_arg = scale;
+  uint32_t epoch = 1;
+  unsigned long long to = 5ull * 1000000000ull;
+  void* kargs[] = {&args, &n_arg, &scale_arg, &epoch, &to};
+  B2_CUDA_CHECK(cudaLaunchCooperativeKernel(fn, dim3(nb, world), dim3(kArThreads), kargs, 0, st));
+  return B2_OK;
+}

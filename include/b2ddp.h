@@ -1,0 +1,189 @@
+/*
+ * b2ddp.h — C ABI of libb2ddp.so: the B200 (sm_100a) kernels for the data-parallel
+ * hot path of valohai/distributed-llms-example (label-masked cross-entropy, AdamW
+ * step, gradient mean all-reduce over NVLink peer memory).
+ *
+ * Conventions
+ *   - every function returns 0 (B2_OK) or a negative b2_status; a human-readable
+ *     message for the calling thread's last failure is at b2_last_error();
+ *   - all data pointers are DEVICE pointers owned by the caller unless the comment
+ *     says "host"; nothing here allocates device memory except b2_comm_create;
+ *   - every launch is asynchronous on the cudaStream_t passed as `stream`
+ *     (a void* here so that the header needs no CUDA include);
+ *   - no torch types cross this boundary; the Python adapters pass
+ *     tensor.data_ptr() and torch.cuda.current_stream().cuda_stream.
+ *
+ * The reference has no native interface of its own (three Python scripts), so
+ * each entry point cites the reference call site whose library kernel it replaces.
+ * SP = site-packages of the image (torch 2.11.0, transformers 5.5.0).
+ */
+#ifndef B2DDP_H
+#define B2DDP_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2DDP_ABI_VERSION 1
+
+typedef void* b2_stream_t; /* cudaStream_t */
+
+enum b2_dtype { B2_F32 = 0, B2_BF16 = 1 };
+
+enum b2_status {
+  B2_OK = 0,
+  B2_ERR_INVALID = -1,   /* bad argument (null pointer, size, alignment, dtype) */
+  B2_ERR_CUDA = -2,      /* a CUDA runtime call failed; message has the cudaError */
+  B2_ERR_STATE = -3,     /* call order (peers not opened, context destroyed...) */
+  B2_ERR_TIMEOUT = -4,   /* a peer did not arrive at a cross-GPU barrier */
+  B2_ERR_TOO_LARGE = -5  /* request exceeds a stated fixed limit */
+};
+
+/* Message of the last failing call made by this host thread ("" if none). */
+const char* b2_last_error(void);
+/* B2DDP_ABI_VERSION the library was built with. */
+int b2_abi_version(void);
+
+/* ------------------------------------------------------------------------- *
+ * (c) label-masked cross-entropy, mean over rows whose label != ignore_index
+ *
+ * Replaces CrossEntropyLoss(ignore_index=-100)(lm_logits.view(-1, V), labels.view(-1))
+ * at SP/transformers/models/t5/modeling_t5.py:1112-1117, reached from
+ * train-accelerator.py:220-221, train-task.py:289-290 and train-torchrun.py:140
+ * (forward), train-accelerator.py:222 / train-task.py:292 (backward).
+ * ------------------------------------------------------------------------- */
+
+/* Bytes of scratch b2_ce_forward needs for (n_rows, vocab): split-row partials
+ * and the arrival counter of its last-block reduction. The counter must be zero
+ * before the first call (cudaMemset the workspace once); the kernel leaves it zero. */
+size_t b2_ce_workspace_bytes(int64_t n_rows, int64_t vocab);
+
+/* logits [n_rows, vocab] row-major, row pitch `row_stride` elements, dtype f32|bf16.
+ * labels [n_rows] int64. Outputs: row_lse[n_rows] fp32 = logsumexp of each row
+ * (written for ignored rows too), loss_out[1] fp32 = sum_valid(lse - z[y]) / n_valid
+ * (NaN when n_valid == 0, like torch), nvalid_out[1] fp32 = n_valid.
+ * A label outside [0, vocab) that is not ignore_index poisons loss_out with NaN
+ * (torch raises a device assert there). Deterministic: fixed reduction order. */
+int b2_ce_forward(const void* logits, const int64_t* labels, int64_t n_rows,
+                  int64_t vocab, int64_t row_stride, int64_t ignore_index, int dtype,
+                  float* row_lse, float* loss_out, float* nvalid_out,
+                  void* workspace, size_t workspace_bytes, b2_stream_t stream);
+
+/* dlogits[i, j] = (exp(z_ij - lse_i) - [j == y_i]) * grad_out / n_valid for valid
+ * rows, 0 for ignored rows, written in the logits dtype with pitch `row_stride`.
+ * grad_out and nvalid are device scalars (no host sync). dlogits must not alias logits. */
+int b2_ce_backward(const void* logits, const int64_t* labels, const float* row_lse,
+                   const float* grad_out, const float* nvalid, int64_t n_rows,
+                   int64_t vocab, int64_t row_stride, int64_t ignore_index, int dtype,
+                   void* dlogits, b2_stream_t stream);
+
+/* ------------------------------------------------------------------------- *
+ * (b) AdamW step over many tensors in one launch
+ *
+ * Replaces torch.optim.AdamW.step (SP/torch/optim/adam.py:215-272 -> _single_tensor_adam
+ * :347-550 / torch._fused_adamw_) called at train-accelerator.py:224, train-task.py:295
+ * and by HF Trainer (SP/transformers/trainer.py:1760) for train-torchrun.py:140.
+ * Per element, all fp32:
+ *   g' = g * (*grad_scale)            (only when grad_scale != NULL: clip fold-in)
+ *   p  = p * (1 - lr*wd)
+ *   m  = m + (1-beta1) * (g' - m)
+ *   v  = v*beta2 + (1-beta2) * g'*g'
+ *   p  = p - (lr/bc1) * m / (sqrt(v)/sqrt(bc2) + eps)
+ * ------------------------------------------------------------------------- */
+
+typedef struct b2_adamw_hyper {
+  double lr;           /* group["lr"] as the host holds it (re-read every step: LambdaLR) */
+  double beta1;
+  double beta2;
+  double eps;
+  double weight_decay;
+  int64_t step;        /* torch's state["step"] AFTER this step's increment (>= 1) */
+} b2_adamw_hyper;
+/* The library derives, in double like adam.py:529-534, then rounds to fp32:
+ *   decay = 1 - lr*wd, w1 = 1 - beta1, 1 - beta2, step_size = lr / (1 - beta1^step),
+ *   bias_correction2_sqrt = sqrt(1 - beta2^step). */
+
+#define B2_ADAMW_MAX_HYPERS 16
+#define B2_ADAMW_CHUNK 8192 /* elements per work item; fixed so plans are portable */
+
+typedef struct b2_adamw_tensor {
+  void* p;             /* fp32 parameter, updated in place */
+  const void* g;       /* fp32 gradient */
+  void* m;             /* fp32 exp_avg, updated in place */
+  void* v;             /* fp32 exp_avg_sq, updated in place */
+  int64_t numel;
+  int32_t hyper;       /* index into the hypers[] passed to b2_adamw_step */
+  int32_t chunk_begin; /* filled by b2_adamw_plan: first work item of this tensor */
+} b2_adamw_tensor;
+
+/* Host-side: fills chunk_begin of tensors_host[0..n) and returns the total number of
+ * work items (ceil(numel / B2_ADAMW_CHUNK) summed), or a negative b2_status. */
+int64_t b2_adamw_plan(b2_adamw_tensor* tensors_host, int32_t n_tensors);
+
+/* tensors_dev: the planned table copied to device memory by the caller.
+ * hypers_host: host array of n_hypers (<= B2_ADAMW_MAX_HYPERS) entries, passed to the
+ * kernel by value (no device copy). grad_scale: device fp32 scalar or NULL. */
+int b2_adamw_step(const b2_adamw_tensor* tensors_dev, int32_t n_tensors,
+                  int64_t total_chunks, const b2_adamw_hyper* hypers_host,
+                  int32_t n_hypers, const float* grad_scale, b2_stream_t stream);
+
+/* One flat partition (p, g, m, v of `numel` fp32 each); no table in device memory. */
+int b2_adamw_step_flat(void* p, const void* g, void* m, void* v, int64_t numel,
+                       const b2_adamw_hyper* hyper_host, const float* grad_scale,
+                       b2_stream_t stream);
+
+/* ------------------------------------------------------------------------- *
+ * (a) gradient mean all-reduce over NVLink peer memory
+ *
+ * Replaces the Reducer's NCCL bucket all-reduce (SP/torch/nn/parallel/distributed.py
+ * :1255-1284 -> default_comm_hooks.hpp:36-51) driven from train-accelerator.py:189,222
+ * and train-torchrun.py:127,140, and the per-tensor dist.all_reduce + "/= size" of
+ * train-task.py:65-69. One process per GPU; the caller moves the 64-byte handles
+ * between processes (torch.distributed all_gather in the Python adapter).
+ * ------------------------------------------------------------------------- */
+
+typedef struct b2_comm b2_comm;
+
+#define B2_IPC_HANDLE_BYTES 64
+#define B2_MAX_WORLD 8
+
+enum b2_algo { B2_ALGO_AUTO = 0, B2_ALGO_ONE_SHOT = 1, B2_ALGO_TWO_SHOT = 2 };
+
+/* Allocates this rank's symmetric staging buffer (2 halves of staging_bytes, used
+ * alternately) and its flag pad on the CURRENT device. world in {1,2,4,8}. */
+int b2_comm_create(int rank, int world, size_t staging_bytes, b2_comm** out);
+/* Writes this rank's B2_IPC_HANDLE_BYTES handle (host memory). */
+int b2_comm_get_handle(b2_comm* c, void* handle_out);
+/* handles: world * B2_IPC_HANDLE_BYTES host bytes in rank order (own slot ignored). */
+int b2_comm_open_peers(b2_comm* c, const void* handles);
+/* Largest numel one b2_allreduce call accepts for a wire dtype. */
+int64_t b2_comm_max_numel(b2_comm* c, int wire_dtype);
+/* buf: fp32 [numel], reduced in place to scale * sum_r buf_r, summed in rank order
+ * 0..W-1 on every rank (bit-identical across ranks and across the two algorithms).
+ * wire_dtype: B2_F32, or B2_BF16 to move bf16 over NVLink (half the bytes; changes
+ * numerics): result = bf16(sum in fp32 of bf16(scale*buf_r)), still stored as fp32.
+ * numel of any size: calls larger than the staging half are chunked internally.
+ * All ranks must call with the same numel/wire/algo in the same order. */
+int b2_allreduce(b2_comm* c, void* buf, int64_t numel, int wire_dtype, float scale,
+                 int algo, b2_stream_t stream);
+/* 0, or B2_ERR_TIMEOUT once a kernel gave up waiting for a peer (sticky). */
+int b2_comm_status(b2_comm* c);
+int b2_comm_destroy(b2_comm* c);
+
+/* Test hook for machines with fewer GPUs than ranks: the same device code run as
+ * ONE launch over `world` virtual ranks whose buffers all live on the current
+ * device (no cross-launch waiting). bufs_host: host array of `world` device
+ * pointers, each fp32 [numel], all reduced in place. staging: device scratch of
+ * b2_allreduce_emulated_scratch_bytes(world, numel) bytes, 256-byte aligned. */
+size_t b2_allreduce_emulated_scratch_bytes(int world, int64_t numel);
+int b2_allreduce_emulated(void* const* bufs_host, int world, int64_t numel,
+                          int wire_dtype, float scale, int algo, void* staging,
+                          b2_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2DDP_H */

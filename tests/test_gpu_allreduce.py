@@ -1,0 +1,175 @@
+"""Gradient all-reduce kernels (-m gpu).
+
+One GPU: the same device code run as ONE cooperative launch over W virtual ranks whose
+buffers all live on cuda:0 (b2_allreduce_emulated) - kernels that wait on one another must
+never be separate launches on one GPU. Two or more GPUs: the real thing, one process per GPU
+over CUDA IPC, plus the DDP comm hook against stock DDP.
+
+Bar: bit-exact against the rank-ordered fp32 sum oracle, and bit-identical on every rank."""
+import ctypes
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ref_numpy as O
+from oracle.inputs import allreduce_inputs
+from oracle.make_golden import ALLREDUCE_CASES
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _L():
+    from distributed_llms_example_b200 import _lib as L
+
+    return L, L.load()
+
+
+def emulated(bufs_np, wire, algo, scale=None):
+    L, lib = _L()
+    w, n = len(bufs_np), bufs_np[0].size
+    bufs = [torch.from_numpy(b.copy()).to(DEV) for b in bufs_np]
+    nbytes = lib.b2_allreduce_emulated_scratch_bytes(w, n)
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=DEV)
+    ptrs = (ctypes.c_void_p * w)(*[b.data_ptr() for b in bufs])
+    L.check(lib.b2_allreduce_emulated(ptrs, w, n, wire, 1.0 / w if scale is None else scale, algo,
+                                      scratch.data_ptr(), torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    return [b.cpu().numpy() for b in bufs]
+
+
+@pytest.mark.parametrize("algo", [1, 2])
+@pytest.mark.parametrize("name", list(ALLREDUCE_CASES))
+def test_emulated_matches_golden_bit_exact(golden, name, algo):
+    w, n, seed = ALLREDUCE_CASES[name]
+    out = emulated(allreduce_inputs(w, n, seed), 0, algo)
+    for r in range(w):
+        np.testing.assert_array_equal(out[r], golden["allreduce"][f"{name}/mean"])
+
+
+@pytest.mark.parametrize("wire", [0, 1])
+@pytest.mark.parametrize("algo", [1, 2])
+@pytest.mark.parametrize("w", [1, 2, 4, 8])
+@pytest.mark.parametrize("n", [1, 3, 4, 1023, 8 * 512 * 4 * 3 + 5, 1 << 20])
+def test_emulated_sizes_wires_algos(w, algo, wire, n):
+    bufs = allreduce_inputs(w, n, 100 + n % 97)
+    out = emulated(bufs, wire, algo)
+    ref = O.allreduce_mean(bufs) if wire == 0 else O.allreduce_mean_bf16_wire(bufs)
+    for r in range(w):
+        np.testing.assert_array_equal(out[r], ref, err_msg=f"rank {r}")
+
+
+def test_emulated_large_bucket_25mib():
+    """A DDP-sized bucket (25 MiB fp32) at W=8, both algorithms give the same bits."""
+    w, n = 8, (25 << 20) // 4
+    bufs = allreduce_inputs(w, n, 7)
+    ref = O.allreduce_mean(bufs)
+    for algo in (1, 2):
+        out = emulated(bufs, 0, algo)
+        for r in range(w):
+            np.testing.assert_array_equal(out[r], ref)
+
+
+def test_comm_world_1_scales_in_place():
+    from distributed_llms_example_b200.comm import P2PComm
+
+    comm = P2PComm()
+    x = torch.randn(100003, device=DEV)
+    ref = (x * 0.5).clone()
+    comm.allreduce_(x, 0.5)
+    torch.cuda.synchronize()
+    assert torch.equal(x, ref)
+    comm.check()
+    comm.close()
+
+
+# ---------------------------------------------------------------------------------------
+# real multi-GPU (needs >= 2 devices; the 1-GPU round-end run skips these)
+# ---------------------------------------------------------------------------------------
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, q):
+    import torch.distributed as dist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from distributed_llms_example_b200.comm import P2PComm, register_p2p_comm_hook
+
+        comm = P2PComm(staging_bytes=8 << 20)
+        results = {}
+        for n in (1, 5, 4096, 1 << 20, (8 << 20) // 4 * 3 + 7):  # the last one is chunked over staging
+            for wire, wname in ((None, "fp32"), ("bf16", "bf16")):
+                for algo in ("one_shot", "two_shot", "auto"):
+                    bufs = allreduce_inputs(world, n, 500 + n % 89)
+                    x = torch.from_numpy(bufs[rank].copy()).cuda()
+                    comm.allreduce_(x, 1.0 / world, wire=wname, algo=algo)
+                    torch.cuda.synchronize()
+                    ref = O.allreduce_mean(bufs) if wname == "fp32" else O.allreduce_mean_bf16_wire(bufs)
+                    results[(n, wname, algo)] = bool(np.array_equal(x.cpu().numpy(), ref))
+        comm.check()
+
+        # DDP comm hook vs stock DDP on the same model / data: 3 steps, identical parameters
+        def run(use_hook):
+            torch.manual_seed(0)
+            model = torch.nn.Sequential(torch.nn.Linear(512, 2048), torch.nn.ReLU(), torch.nn.Linear(2048, 4096),
+                                        torch.nn.ReLU(), torch.nn.Linear(4096, 512)).cuda()
+            ddp = torch.nn.parallel.DistributedDataParallel(model, device_ids=[rank], bucket_cap_mb=4)
+            if use_hook:
+                register_p2p_comm_hook(ddp, comm=comm)
+            opt = torch.optim.SGD(ddp.parameters(), lr=0.1)
+            g = torch.Generator(device="cuda").manual_seed(1234 + rank)
+            for _ in range(3):
+                x = torch.randn(16, 512, device="cuda", generator=g)
+                ddp(x).square().mean().backward()
+                opt.step(); opt.zero_grad()
+            return [p.detach().clone() for p in model.parameters()]
+
+        a, b = run(True), run(False)
+        worst = max(float(((x - y).abs() / (y.abs() + 1e-6)).max()) for x, y in zip(a, b))
+        # replicas must stay bit-identical across ranks
+        same = True
+        for p in a:
+            gathered = [torch.empty_like(p) for _ in range(world)]
+            dist.all_gather(gathered, p)
+            same &= all(torch.equal(gathered[0], t) for t in gathered)
+        comm.close()
+        q.put((rank, results, worst, same, None))
+    except Exception as exc:  # surface the failure in the parent
+        import traceback
+
+        q.put((rank, {}, 0.0, False, traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs (run with gpurun --gpus 2)")
+def test_real_peer_memory_allreduce_and_ddp_hook():
+    import torch.multiprocessing as mp
+
+    world = 2 if torch.cuda.device_count() < 4 else (4 if torch.cuda.device_count() < 8 else 8)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    outs = [q.get(timeout=600) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, results, worst, same, err in outs:
+        assert err is None, f"rank {rank}:\n{err}"
+        bad = [k for k, ok in results.items() if not ok]
+        assert not bad, f"rank {rank}: not bit-exact vs the rank-ordered oracle: {bad}"
+        assert worst < 1e-6, f"rank {rank}: hook vs stock DDP parameters differ by {worst}"
+        assert same, f"rank {rank}: replicas diverged"
