@@ -186,7 +186,6 @@ def test_adamw_full_size_flan_t5_large_layout():
             a.grad = torch.randn_like(a) * 1e-2
             b.grad = a.grad
         o.step(); t.step()
-    worst = 0.0
+    # |update| ~ lr = 5e-5 per step, so 1e-9 absolute is 2e-5 of one update
     for a, b in zip(ours, theirs):
-        worst = max(worst, float(((a - b).abs() / (b.abs() + 1e-6)).max()))
-    assert worst < 1e-5, worst
+        torch.testing.assert_close(a.detach(), b.detach(), rtol=1e-6, atol=1e-9)

@@ -108,13 +108,19 @@ def test_ce_module_is_a_drop_in_for_t5_loss():
     assert loss.dtype == torch.float32 and loss.dim() == 0
     loss.backward()
     assert lm_logits.grad.dtype == torch.bfloat16 and lm_logits.grad.shape == lm_logits.shape
-    ref_in = lm_logits.detach().clone().requires_grad_(True)
-    with torch.autocast("cuda", dtype=torch.bfloat16):
-        ref = torch.nn.CrossEntropyLoss(ignore_index=-100)(ref_in.view(-1, v), labels.view(-1))
+    # Oracle = the same bf16 values up-cast to fp32. torch's own autocast path
+    # rounds log-probabilities to bf16 on this image and is ~1e-4 off the fp32 answer, so it
+    # is only checked loosely.
+    ref_in = lm_logits.detach().float().requires_grad_(True)
+    ref = torch.nn.CrossEntropyLoss(ignore_index=-100)(ref_in.view(-1, v), labels.view(-1))
     ref.backward()
     torch.testing.assert_close(loss, ref, rtol=1e-5, atol=0)
-    diff = (lm_logits.grad.float() - ref_in.grad.float()).abs()
-    assert bool((diff <= ref_in.grad.float().abs() * 2.0 ** -7 + 1e-12).all())
+    diff = (lm_logits.grad.float() - ref_in.grad).abs()
+    assert bool((diff <= ref_in.grad.abs() * 2.0 ** -8 + 1e-12).all())
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        stock = torch.nn.CrossEntropyLoss(ignore_index=-100)(lm_logits.detach().view(-1, v), labels.view(-1))
+    assert stock.dtype == torch.float32
+    torch.testing.assert_close(loss, stock, rtol=2e-3, atol=0)
     assert bool((lm_logits.grad.view(-1, v)[labels.view(-1) == -100] == 0).all())
 
 
