@@ -104,6 +104,9 @@ class P2PComm:
                 dist.barrier(self.group)  # nobody unmaps while a peer may still read
             self._lib.b2_comm_destroy(self._ctx)
             self._ctx = None
+        global _default
+        if _default is self:
+            _default = None
 
     def __del__(self):  # best effort; explicit close() is the collective-safe way
         try:
@@ -183,6 +186,4 @@ def average_gradients(model: torch.nn.Module, comm: Optional[P2PComm] = None) ->
         raise NotImplementedError("average_gradients: fp32 gradients only")
     flat = torch.cat([g.reshape(-1) for g in grads])
     comm.allreduce_(flat, 1.0 / comm.world)
-    torch._foreach_copy_([g.view(-1) if g.is_contiguous() else g for g in grads],
-                         [c.view_as(g) if not g.is_contiguous() else c
-                          for c, g in zip(flat.split([g.numel() for g in grads]), grads)])
+    torch._foreach_copy_(grads, [c.view_as(g) for c, g in zip(flat.split([g.numel() for g in grads]), grads)])

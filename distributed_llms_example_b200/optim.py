@@ -68,6 +68,9 @@ class AdamW(Optimizer):
         #: optional device fp32 scalar multiplied into every gradient inside the kernel
         #: (gradient-clipping fold-in); set by clip helpers, cleared after each step.
         self.grad_scale: Optional[torch.Tensor] = None
+        #: when set to a list, step() appends a (start, end) CUDA event pair recorded on the
+        #: launching stream tightly around the kernel launch (bench.py's roofline timing).
+        self.kernel_events: Optional[list] = None
 
     def __setstate__(self, state: dict[str, Any]) -> None:
         super().__setstate__(state)
@@ -172,10 +175,17 @@ class AdamW(Optimizer):
             gs = self.grad_scale
             if gs is not None and (gs.dtype != torch.float32 or gs.device != device or gs.numel() != 1):
                 raise ValueError("grad_scale must be a 1-element fp32 tensor on the parameters' device")
+            ev = None
+            if self.kernel_events is not None:
+                ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+                ev[0].record()
             _lib.check(self._lib.b2_adamw_step(
                 self._table_dev.data_ptr(), self._n_tensors, self._total_chunks, hp, len(hypers),
                 gs.data_ptr() if gs is not None else None,
                 torch.cuda.current_stream(device).cuda_stream))
             _lib.count_launch()
+            if ev is not None:
+                ev[1].record()
+                self.kernel_events.append(ev)
         self.grad_scale = None
         return loss

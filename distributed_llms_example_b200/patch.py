@@ -1,0 +1,90 @@
+"""Attaches the three plug-ins through public names, without editing the reference scripts.
+
+Patch points
+  * ``transformers.models.<family>.modeling_<family>.CrossEntropyLoss``: T5 (and BART, the
+    default ``model_ckpt`` of valohai.yaml:8-20) build their loss from this module-level name
+    (modeling_t5.py:21,1114), so rebinding it touches nothing else;
+  * ``torch.optim.AdamW``: the scripts execute ``from torch.optim import AdamW`` at import
+    (train-accelerator.py:14, train-task.py:17) and HF Trainer resolves it lazily
+    (trainer_optimizer.py:203), so it must be rebound before the script module runs;
+  * ``DistributedDataParallel.__init__``: registers the comm hook right after construction,
+    because Accelerate's ``DistributedDataParallelKwargs(comm_hook=...)`` only carries built-in
+    enum hooks;
+  * ``average_gradients`` of train-task.py:65-69 is a function of the script itself; launch.py
+    rebinds it in the script's namespace right after its definition.
+"""
+from __future__ import annotations
+
+import importlib
+from typing import Any
+
+import torch
+
+_CE_MODULES = ("transformers.models.t5.modeling_t5", "transformers.models.bart.modeling_bart")
+_saved: dict[str, Any] = {}
+
+
+def patch_cross_entropy() -> None:
+    from .loss import CrossEntropyLoss
+
+    for name in _CE_MODULES:
+        try:
+            mod = importlib.import_module(name)
+        except ImportError:
+            continue
+        if hasattr(mod, "CrossEntropyLoss"):
+            _saved.setdefault(f"ce:{name}", mod.CrossEntropyLoss)
+            mod.CrossEntropyLoss = CrossEntropyLoss
+
+
+def patch_adamw() -> None:
+    from .optim import AdamW
+
+    _saved.setdefault("adamw", torch.optim.AdamW)
+    torch.optim.AdamW = AdamW
+
+
+def patch_ddp(**comm_kwargs) -> None:
+    """Every DistributedDataParallel built afterwards on a CUDA device with world size > 1 gets
+    the peer-memory all-reduce hook."""
+    from torch.nn.parallel import DistributedDataParallel as DDP
+
+    if "ddp_init" in _saved:
+        return
+    orig = DDP.__init__
+    _saved["ddp_init"] = orig
+
+    def __init__(self, module, *args, **kwargs):
+        orig(self, module, *args, **kwargs)
+        import torch.distributed as dist
+
+        first = next(module.parameters(), None)
+        if first is not None and first.is_cuda and dist.get_world_size(self.process_group) > 1:
+            from .comm import register_p2p_comm_hook
+
+            self._b200_hook_state = register_p2p_comm_hook(self, **comm_kwargs)
+
+    DDP.__init__ = __init__
+
+
+def apply(cross_entropy: bool = True, adamw: bool = True, ddp: bool = True) -> None:
+    if cross_entropy:
+        patch_cross_entropy()
+    if adamw:
+        patch_adamw()
+    if ddp:
+        patch_ddp()
+
+
+def remove() -> None:
+    """Undo apply() (used by the benchmark to time the stock path in the same process)."""
+    from torch.nn.parallel import DistributedDataParallel as DDP
+
+    for key, val in list(_saved.items()):
+        if key.startswith("ce:"):
+            importlib.import_module(key[3:]).CrossEntropyLoss = val
+        elif key == "adamw":
+            torch.optim.AdamW = val
+        elif key == "ddp_init":
+            DDP.__init__ = val
+        del _saved[key]
