@@ -14,6 +14,7 @@ B2_IPC_HANDLE_BYTES = 64
 B2_MAX_WORLD = 8
 B2_ADAMW_MAX_HYPERS = 16
 B2_ADAMW_CHUNK = 8192
+B2_CE_NOALLOC_MAX_ROWS = 8192
 ABI_VERSION = 1
 
 
@@ -43,6 +44,7 @@ SIGNATURES = {
     "b2_abi_version": (C.c_int, []),
     "b2_ce_workspace_bytes": (_sz, [_i64, _i64]),
     "b2_ce_forward": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _i32, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "b2_ce_forward_noalloc": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _i32, _vp, _vp, _vp, _vp]),
     "b2_ce_backward": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _i32, _vp, _vp]),
     "b2_adamw_plan": (_i64, [C.POINTER(AdamWTensor), C.c_int32]),
     "b2_adamw_step": (C.c_int, [_vp, C.c_int32, _i64, C.POINTER(AdamWHyper), C.c_int32, _vp, _vp]),

@@ -400,3 +400,98 @@ extern "C" int b2_ce_backward(const void* logits, const int64_t* labels, const f
   B2_CUDA_CHECK(cudaGetLastError());
   return B2_OK;
 }
+
+// ---------------------------------------------------------------------------------------
+// b2_ce_forward_noalloc: the forward above for hosts that must not allocate.
+//
+// Some programs that embed this library cannot give it a workspace: a serving or training
+// runtime that reserves the whole device for its own pool at start-up (a later cudaMalloc
+// fails, or is forbidden by policy once the job is "warm"), or a thin foreign-language
+// binding that has no place to keep a buffer alive between calls. For them the scratch
+// lives inside the library image itself: a file-scope __device__ array of fixed size,
+// present on every GPU that loads libb2ddp.so until the process exits.
+//
+// The array's name is only a host-side handle for the symbol, not a device address, so the
+// host asks the runtime for the address once per device (cudaGetSymbolAddress, with that
+// device current) and hands THAT pointer to the kernel. The first call on a device performs
+// this set-up; make that first call before any stream capture begins.
+//
+// All calls on a device share the one array and it keeps whatever the previous call left
+// in it, so the arrival counter is cleared on the stream before every launch. Two calls
+// whose kernels overlap on the GPU (different streams, no ordering between them) race on
+// the scratch and produce garbage: serialise them. No cudaMalloc / cudaFree / allocating
+// library routine is called on this path.
+// ---------------------------------------------------------------------------------------
+
+namespace b2 {
+
+constexpr size_t kNoAllocScratchBytes =
+    16 + (size_t)B2_CE_NOALLOC_MAX_ROWS * 4 +
+    (size_t)B2_CE_NOALLOC_MAX_ROWS * kCeMaxSplit * sizeof(MS);  // 1 081 360 B
+
+static __device__ __align__(256) unsigned char g_ce_noalloc_scratch[kNoAllocScratchBytes];
+
+constexpr int kMaxDevices = 64;
+static void* g_noalloc_ptr[kMaxDevices] = {nullptr};  // device address of the array, per device
+
+// Device address of the scratch array on the current device (resolved once per device).
+static int noalloc_scratch(void** out) {
+  int dev = -1;
+  B2_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices)
+    return fail(B2_ERR_INVALID, "ce_forward_noalloc: device ordinal %d outside [0, %d)", dev, kMaxDevices);
+  void* p = __atomic_load_n(&g_noalloc_ptr[dev], __ATOMIC_ACQUIRE);
+  if (!p) {
+    B2_CUDA_CHECK(cudaGetSymbolAddress(&p, g_ce_noalloc_scratch));
+    if (!p) return fail(B2_ERR_CUDA, "ce_forward_noalloc: cudaGetSymbolAddress returned a null address");
+    __atomic_store_n(&g_noalloc_ptr[dev], p, __ATOMIC_RELEASE);  // same value from any thread
+  }
+  *out = p;
+  return B2_OK;
+}
+
+}  // namespace b2
+
+extern "C" int b2_ce_forward_noalloc(const void* logits, const int64_t* labels, int64_t n_rows,
+                                     int64_t vocab, int64_t row_stride, int64_t ignore_index,
+                                     int dtype, float* row_lse, float* loss_out, float* nvalid_out,
+                                     b2_stream_t stream) {
+  using namespace b2;
+  B2_REQUIRE(dtype == B2_F32 || dtype == B2_BF16, "ce_forward_noalloc: dtype %d not f32/bf16", dtype);
+  B2_REQUIRE(n_rows >= 0 && vocab > 0 && vocab < (1ll << 30), "ce_forward_noalloc: bad shape [%lld, %lld]",
+             (long long)n_rows, (long long)vocab);
+  if (n_rows > B2_CE_NOALLOC_MAX_ROWS)
+    return fail(B2_ERR_TOO_LARGE,
+                "ce_forward_noalloc: %lld rows exceed the built-in scratch (max %d rows); use "
+                "b2_ce_forward with a caller-provided workspace",
+                (long long)n_rows, B2_CE_NOALLOC_MAX_ROWS);
+  B2_REQUIRE(row_stride >= vocab, "ce_forward_noalloc: row_stride %lld < vocab %lld",
+             (long long)row_stride, (long long)vocab);
+  B2_REQUIRE(loss_out && nvalid_out, "ce_forward_noalloc: null output");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n_rows == 0) {
+    static const float kNan = __builtin_nanf(""), kZero = 0.f;
+    B2_CUDA_CHECK(cudaMemcpyAsync(loss_out, &kNan, 4, cudaMemcpyHostToDevice, st));
+    B2_CUDA_CHECK(cudaMemcpyAsync(nvalid_out, &kZero, 4, cudaMemcpyHostToDevice, st));
+    return B2_OK;
+  }
+  B2_REQUIRE(logits && labels && row_lse, "ce_forward_noalloc: null pointer");
+  void* ws = nullptr;
+  int rc = noalloc_scratch(&ws);
+  if (rc != B2_OK) return rc;
+  // The array still holds the previous call's contents; only the counter has to be zero.
+  B2_CUDA_CHECK(cudaMemsetAsync(ws, 0, 16, st));
+  const int split = pick_split(n_rows);
+  const long long grid = n_rows * split;
+  if (dtype == B2_BF16) {
+    ce_forward_kernel<true><<<(unsigned)grid, kCeThreads, 0, st>>>(
+        (const __nv_bfloat16*)logits, (const long long*)labels, n_rows, (int)vocab, row_stride,
+        ignore_index, split, row_lse, loss_out, nvalid_out, ws);
+  } else {
+    ce_forward_kernel<false><<<(unsigned)grid, kCeThreads, 0, st>>>(
+        (const float*)logits, (const long long*)labels, n_rows, (int)vocab, row_stride,
+        ignore_index, split, row_lse, loss_out, nvalid_out, ws);
+  }
+  B2_CUDA_CHECK(cudaGetLastError());
+  return B2_OK;
+}

@@ -72,6 +72,24 @@ int b2_ce_forward(const void* logits, const int64_t* labels, int64_t n_rows,
                   float* row_lse, float* loss_out, float* nvalid_out,
                   void* workspace, size_t workspace_bytes, b2_stream_t stream);
 
+/* No counterpart in the reference: an addition for hosts that cannot allocate device
+ * memory. Same computation and outputs as b2_ce_forward, but the scratch is a fixed array
+ * inside the library image instead of a caller workspace, so this path performs no
+ * cudaMalloc/cudaFree and takes no workspace argument. Meant for embedders whose runtime
+ * owns all device memory after start-up (an allocation would fail or is not permitted) and
+ * for thin bindings with nowhere to keep a workspace alive between calls.
+ *   - at most B2_CE_NOALLOC_MAX_ROWS rows per call; more returns B2_ERR_TOO_LARGE;
+ *   - the first call on each device resolves the array's device address (with that device
+ *     current); make that first call before any stream capture starts;
+ *   - one array per device shared by every call: calls whose kernels may overlap on the GPU
+ *     (unordered streams) race on it and must be serialised by the caller;
+ *   - the array costs about 1.03 MiB on every GPU that loads the library, until exit. */
+#define B2_CE_NOALLOC_MAX_ROWS 8192
+int b2_ce_forward_noalloc(const void* logits, const int64_t* labels, int64_t n_rows,
+                          int64_t vocab, int64_t row_stride, int64_t ignore_index, int dtype,
+                          float* row_lse, float* loss_out, float* nvalid_out,
+                          b2_stream_t stream);
+
 /* dlogits[i, j] = (exp(z_ij - lse_i) - [j == y_i]) * grad_out / n_valid for valid
  * rows, 0 for ignored rows, written in the logits dtype with pitch `row_stride`.
  * grad_out and nvalid are device scalars (no host sync). dlogits must not alias logits. */
