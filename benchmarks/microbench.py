@@ -1,0 +1,235 @@
+#!/usr/bin/env python
+"""Kernel microbenchmarks of BASELINE config 4: AdamW over the real tensor-size lists, masked CE
+over N x 32128, and the all-reduce bucket sweep, each next to the stock library kernel it replaces.
+
+    python benchmarks/microbench.py adamw  [--models t5-small flan-t5-base flan-t5-large flan-t5-xl]
+    python benchmarks/microbench.py ce     [--rows 128 1024 8192 32768]
+    torchrun --nproc-per-node N benchmarks/microbench.py allreduce [--sizes-mb 1 2 4 ...]
+
+Timing: CUDA events on the launching stream, warm-up then median of --iters; between timed
+iterations a 512 MB buffer is written to flush the 126 MB L2 whenever the kernel's working set
+could fit in it (CE at small N); AdamW and large buckets exceed L2 by themselves. One JSON line
+per measurement. `--only ours` keeps the run short for ncu.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+PEAK = 6549.8
+try:
+    PEAK = float(json.loads((ROOT / "MEASURED_PEAKS.json").read_text())["hbm_gbs"])
+except Exception:
+    pass
+
+_flush = None
+
+
+def flush_l2():
+    global _flush
+    if _flush is None:
+        _flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")
+    _flush.zero_()
+
+
+def time_ms(fn, iters: int, warmup: int, flush: bool):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(iters):
+        if flush:
+            flush_l2()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        b.synchronize()
+        ts.append(a.elapsed_time(b))
+    return statistics.median(ts), min(ts)
+
+
+def emit(**kw):
+    print(json.dumps(kw), flush=True)
+
+
+# ------------------------------------------------------------------------------------------
+def bench_adamw(args):
+    from distributed_llms_example_b200.optim import AdamW
+    from distributed_llms_example_b200.synthetic import build_model
+
+    for name in args.models:
+        with torch.device("meta"):
+            shapes = [tuple(p.shape) for p in build_model(name).parameters()]
+        n = sum(int(np.prod(s)) for s in shapes)
+        torch.manual_seed(0)
+        ps = [torch.nn.Parameter(torch.randn(s, device="cuda") * 0.02) for s in shapes]
+        for p in ps:
+            p.grad = torch.randn_like(p) * 1e-2
+        impls = {"b200": lambda: AdamW(ps, lr=5e-5, weight_decay=0.01)}
+        if args.only != "ours":
+            impls["torch_fused"] = lambda: torch.optim.AdamW(ps, lr=5e-5, weight_decay=0.01, fused=True)
+            impls["torch_foreach"] = lambda: torch.optim.AdamW(ps, lr=5e-5, weight_decay=0.01, foreach=True)
+        for impl, make in impls.items():
+            opt = make()
+            if impl == "b200":
+                # kernel-only time (events tight around the launch) and whole step() call
+                opt.kernel_events = []
+                med, best = time_ms(opt.step, args.iters, args.warmup, False)
+                torch.cuda.synchronize()
+                k = [a.elapsed_time(b) for a, b in opt.kernel_events[args.warmup:]]
+                kmed = statistics.median(k)
+                emit(bench="adamw", model=name, impl=impl, params=n, tensors=len(shapes), step_call_ms=med,
+                     kernel_ms=kmed, gbs=28 * n / kmed / 1e6, frac_measured_peak=28 * n / kmed / 1e6 / PEAK,
+                     frac_8tbs=28 * n / kmed / 1e6 / 8000, launches_per_step=1)
+            else:
+                med, best = time_ms(opt.step, args.iters, args.warmup, False)
+                emit(bench="adamw", model=name, impl=impl, params=n, tensors=len(shapes), step_call_ms=med,
+                     gbs=28 * n / med / 1e6, frac_measured_peak=28 * n / med / 1e6 / PEAK)
+            del opt
+        del ps
+        torch.cuda.empty_cache()
+
+
+# ------------------------------------------------------------------------------------------
+def bench_ce(args):
+    from distributed_llms_example_b200.loss import cross_entropy
+
+    v = 32128
+    for tdt, s in ((torch.bfloat16, 2), (torch.float32, 4)):
+        for n in args.rows:
+            if n * v * s > 6 << 30:
+                continue
+            torch.manual_seed(0)
+            z = (torch.randn(n, v, device="cuda") * 4).to(tdt).requires_grad_(True)
+            y = torch.randint(0, v, (n,), device="cuda")
+            y[torch.rand(n, device="cuda") < 0.2] = -100
+            flush = 3 * n * v * s < (256 << 20)
+            frac_valid = float((y != -100).float().mean())
+
+            def ours_fwd():
+                return cross_entropy(z, y)
+
+            loss = ours_fwd()
+
+            def ours_bwd():
+                z.grad = None
+                loss.backward(retain_graph=True)
+
+            fmed, _ = time_ms(ours_fwd, args.iters, args.warmup, flush)
+            bmed, _ = time_ms(ours_bwd, args.iters, args.warmup, flush)
+            fb, bb = n * v * s, n * v * s * (1 + frac_valid)  # backward reads only the valid rows
+            emit(bench="ce", dtype=str(tdt).split(".")[-1], rows=n, impl="b200", l2_flush=flush, fwd_ms=fmed,
+                 bwd_ms=bmed, fwd_gbs=fb / fmed / 1e6, bwd_gbs=bb / bmed / 1e6,
+                 fwd_frac_measured_peak=fb / fmed / 1e6 / PEAK, bwd_frac_measured_peak=bb / bmed / 1e6 / PEAK,
+                 fwd_bwd_ms=fmed + bmed)
+            if args.only == "ours":
+                continue
+            z.grad = None
+
+            def stock_fwd():
+                with torch.autocast("cuda", dtype=torch.bfloat16, enabled=(tdt == torch.bfloat16)):
+                    return torch.nn.functional.cross_entropy(z, y, ignore_index=-100)
+
+            sloss = stock_fwd()
+
+            def stock_bwd():
+                z.grad = None
+                sloss.backward(retain_graph=True)
+
+            sf, _ = time_ms(stock_fwd, args.iters, args.warmup, flush)
+            sb, _ = time_ms(stock_bwd, args.iters, args.warmup, flush)
+            emit(bench="ce", dtype=str(tdt).split(".")[-1], rows=n, impl="torch", l2_flush=flush, fwd_ms=sf,
+                 bwd_ms=sb, fwd_bwd_ms=sf + sb, speedup_fwd_bwd=(sf + sb) / (fmed + bmed))
+            del z, y
+            torch.cuda.empty_cache()
+
+
+# ------------------------------------------------------------------------------------------
+def bench_allreduce(args):
+    from distributed_llms_example_b200.comm import P2PComm
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    comm = P2PComm(staging_bytes=args.staging_mb << 20)
+
+    def timed(fn, iters, warmup):
+        for _ in range(warmup):
+            fn()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(iters):
+            fn()
+        b.record()
+        b.synchronize()
+        t = torch.tensor([a.elapsed_time(b) / iters], device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    for mb in args.sizes_mb:
+        n = int(mb * (1 << 20)) // 4
+        x = torch.randn(n, device="cuda") * 1e-2
+        iters = max(5, min(args.iters, int(2000 / max(mb, 1))))
+        rows = []
+        for wire in args.wires:
+            for algo in args.algos:
+                if world == 1 and algo != "auto":
+                    continue
+                ms = timed(lambda: comm.allreduce_(x, 1.0 / world, wire=wire, algo=algo), iters, args.warmup)
+                rows.append((f"b200_{wire}_{algo}", ms))
+        if world > 1 and args.only != "ours":
+            def nccl():
+                x.div_(world)
+                dist.all_reduce(x)
+            rows.append(("nccl_div_allreduce", timed(nccl, iters, args.warmup)))
+            rows.append(("nccl_allreduce_only", timed(lambda: dist.all_reduce(x), iters, args.warmup)))
+        if rank == 0:
+            for impl, ms in rows:
+                bus = n * 4 * 2 * (world - 1) / world / ms / 1e6 if world > 1 else 0.0
+                emit(bench="allreduce", world=world, size_mb=mb, impl=impl, ms=ms, bus_gbs=bus,
+                     frac_of_900=bus / 900.0, alg_gbs=n * 4 / ms / 1e6)
+        del x
+    comm.check()
+    comm.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("bench", choices=["adamw", "ce", "allreduce"])
+    ap.add_argument("--models", nargs="+", default=["t5-small", "flan-t5-base", "flan-t5-large", "flan-t5-xl"])
+    ap.add_argument("--rows", nargs="+", type=int, default=[128, 1024, 8192, 32768])
+    ap.add_argument("--sizes-mb", nargs="+", type=float, default=[1, 2, 4, 8, 16, 25, 32, 64, 128, 256, 512, 1024])
+    ap.add_argument("--wires", nargs="+", default=["fp32", "bf16"])
+    ap.add_argument("--algos", nargs="+", default=["auto", "one_shot", "two_shot"])
+    ap.add_argument("--staging-mb", type=int, default=64)
+    ap.add_argument("--iters", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--only", default="all", choices=["all", "ours"])
+    args = ap.parse_args()
+    {"adamw": bench_adamw, "ce": bench_ce, "allreduce": bench_allreduce}[args.bench](args)
+
+
+if __name__ == "__main__":
+    main()

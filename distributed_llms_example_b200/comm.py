@@ -13,8 +13,6 @@ The torch.distributed process group stays the control plane (rendezvous, handle 
 barriers); only gradient bytes move through libb2ddp's kernels. Single node, world in
 {1, 2, 4, 8}. No NCCL/gloo fallback for the data path.
 """
-from __future__ import annotations
-
 import ctypes as C
 import os
 from typing import Optional
@@ -117,7 +115,7 @@ class P2PComm:
             pass
 
 
-_default: Optional[P2PComm] = None
+_default: Optional["P2PComm"] = None
 
 
 def default_comm(**kwargs) -> P2PComm:
