@@ -157,6 +157,71 @@ def bench_ce(args):
 
 
 # ------------------------------------------------------------------------------------------
+def bench_ce_kernel(args):
+    """Kernel-only CE timing straight through the C ABI: `reps` back-to-back launches between two
+    events, rotating over enough distinct input buffers that the rotation exceeds the 126 MB L2
+    (so small batches are measured cold, like they are inside a training step)."""
+    from distributed_llms_example_b200 import _lib as L
+
+    lib = L.load()
+    v = 32128
+    stream = torch.cuda.current_stream().cuda_stream
+    for tdt, s, code in ((torch.bfloat16, 2, L.B2_BF16), (torch.float32, 4, L.B2_F32)):
+        for n in args.rows:
+            nbuf = max(2, min(64, -(-(400 << 20) // (n * v * s))))
+            if nbuf * n * v * s * 2 > 60 << 30:
+                nbuf = 2
+            torch.manual_seed(0)
+            zs = [(torch.randn(n, v, device="cuda") * 4).to(tdt) for _ in range(nbuf)]
+            ds = [torch.empty_like(z) for z in zs]
+            y = torch.randint(0, v, (n,), device="cuda")
+            y[torch.rand(n, device="cuda") < 0.2] = -100
+            frac_valid = float((y != -100).float().mean())
+            lse = torch.empty(n, device="cuda")
+            loss = torch.empty(1, device="cuda")
+            nvalid = torch.empty(1, device="cuda")
+            g = torch.ones(1, device="cuda")
+            nb = lib.b2_ce_workspace_bytes(n, v)
+            ws = torch.zeros(nb, dtype=torch.uint8, device="cuda")
+            reps = max(nbuf, 8)
+
+            def fwd(i):
+                z = zs[i % nbuf]
+                L.check(lib.b2_ce_forward(z.data_ptr(), y.data_ptr(), n, v, v, -100, code, lse.data_ptr(),
+                                          loss.data_ptr(), nvalid.data_ptr(), ws.data_ptr(), nb, stream))
+
+            def bwd(i):
+                z, d = zs[i % nbuf], ds[i % nbuf]
+                L.check(lib.b2_ce_backward(z.data_ptr(), y.data_ptr(), lse.data_ptr(), g.data_ptr(),
+                                           nvalid.data_ptr(), n, v, v, -100, code, d.data_ptr(), stream))
+
+            def run(fn):
+                for i in range(reps):
+                    fn(i)
+                torch.cuda.synchronize()
+                ts = []
+                for _ in range(args.iters):
+                    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a.record()
+                    for i in range(reps):
+                        fn(i)
+                    b.record()
+                    b.synchronize()
+                    ts.append(a.elapsed_time(b) / reps)
+                return statistics.median(ts)
+
+            fwd(0)
+            f_ms, b_ms = run(fwd), run(bwd)
+            fb, bb = n * v * s, n * v * s * (1 + frac_valid)
+            emit(bench="ce_kernel", dtype=str(tdt).split(".")[-1], rows=n, buffers=nbuf, reps=reps,
+                 fwd_us=f_ms * 1e3, bwd_us=b_ms * 1e3, fwd_gbs=fb / f_ms / 1e6, bwd_gbs=bb / b_ms / 1e6,
+                 fwd_frac_measured_peak=fb / f_ms / 1e6 / PEAK, bwd_frac_measured_peak=bb / b_ms / 1e6 / PEAK,
+                 env={k: os.environ[k] for k in os.environ if k.startswith("B2_CE")})
+            del zs, ds
+            torch.cuda.empty_cache()
+
+
+# ------------------------------------------------------------------------------------------
 def bench_allreduce(args):
     from distributed_llms_example_b200.comm import P2PComm
 
@@ -217,7 +282,7 @@ def bench_allreduce(args):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("bench", choices=["adamw", "ce", "allreduce"])
+    ap.add_argument("bench", choices=["adamw", "ce", "ce_kernel", "allreduce"])
     ap.add_argument("--models", nargs="+", default=["t5-small", "flan-t5-base", "flan-t5-large", "flan-t5-xl"])
     ap.add_argument("--rows", nargs="+", type=int, default=[128, 1024, 8192, 32768])
     ap.add_argument("--sizes-mb", nargs="+", type=float, default=[1, 2, 4, 8, 16, 25, 32, 64, 128, 256, 512, 1024])
@@ -228,7 +293,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--only", default="all", choices=["all", "ours"])
     args = ap.parse_args()
-    {"adamw": bench_adamw, "ce": bench_ce, "allreduce": bench_allreduce}[args.bench](args)
+    {"adamw": bench_adamw, "ce": bench_ce, "ce_kernel": bench_ce_kernel, "allreduce": bench_allreduce}[args.bench](args)
 
 
 if __name__ == "__main__":

@@ -12,6 +12,9 @@
 //            counter + row losses + split partials).
 // Backward : one read + one write of N*V elements; ignored rows are written as zeros
 //            without reading their logits.
+#include <algorithm>
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace b2 {
@@ -98,32 +101,6 @@ __host__ __device__ inline CeScratch carve(void* ws, long long n_rows) {
   return s;
 }
 
-__device__ __forceinline__ MS block_merge(MS st, MS* smem) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    MS other;
-    other.m = __shfl_xor_sync(0xffffffffu, st.m, o);
-    other.s = __shfl_xor_sync(0xffffffffu, st.s, o);
-    st = ms_merge(st, other);
-  }
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (lane == 0) smem[warp] = st;
-  __syncthreads();
-  if (warp == 0) {
-    constexpr int kWarps = kCeThreads / 32;
-    MS v = lane < kWarps ? smem[lane] : MS{-INFINITY, 0.f};
-#pragma unroll
-    for (int o = kWarps / 2; o > 0; o >>= 1) {
-      MS other;
-      other.m = __shfl_xor_sync(0xffffffffu, v.m, o);
-      other.s = __shfl_xor_sync(0xffffffffu, v.s, o);
-      v = ms_merge(v, other);
-    }
-    st = v;
-  }
-  return st;  // valid in warp 0
-}
-
 __device__ __forceinline__ float block_sum(float v, float* smem) {
   v = warp_sum(v);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -138,8 +115,76 @@ __device__ __forceinline__ float block_sum(float v, float* smem) {
   return v;  // valid in thread 0
 }
 
+// Largest element of U raw 16-byte packs. bf16: packed HMNMX2 on the raw words (max is exact in
+// bf16), one unpack at the end; fp32: plain fmaxf chain (ptxas fuses pairs into 3-input FMNMX).
+template <bool BF16, int U>
+__device__ __forceinline__ float packs_max(const uint4 (&r)[U]) {
+  if constexpr (BF16) {
+    __nv_bfloat162 m = *reinterpret_cast<const __nv_bfloat162*>(&r[0].x);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const uint32_t w[4] = {r[u].x, r[u].y, r[u].z, r[u].w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) m = __hmax2(m, *reinterpret_cast<const __nv_bfloat162*>(&w[k]));
+    }
+    const uint32_t mw = *reinterpret_cast<uint32_t*>(&m);
+    return fmaxf(bf16lo(mw), bf16hi(mw));
+  } else {
+    float m = __uint_as_float(r[0].x);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      m = fmaxf(m, fmaxf(__uint_as_float(r[u].x), __uint_as_float(r[u].y)));
+      m = fmaxf(m, fmaxf(__uint_as_float(r[u].z), __uint_as_float(r[u].w)));
+    }
+    return m;
+  }
+}
+
+// st <- st merged with the U packs in r: one FFMA + one MUFU.EX2 + one FADD per element.
+// exp(x - ref) is evaluated as ex2(x*log2e - ref*log2e); NaN inputs propagate (hmax2/fmaxf drop
+// NaN from the max, but ex2(NaN) lands in the sum).
+template <bool BF16, int U>
+__device__ __forceinline__ void ms_update_packs(MS& st, const uint4 (&r)[U]) {
+  using E = Elem<BF16>;
+  const float m = fmaxf(st.m, packs_max<BF16, U>(r));
+  const float ref = safe_ref(m);
+  const float neg = -ref * kLog2e;
+  float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    float x[E::kPerPack];
+    E::unpack(r[u], x);
+#pragma unroll
+    for (int k = 0; k < E::kPerPack; k += 2) {
+      acc0 += fast_exp2(fmaf(x[k], kLog2e, neg));
+      acc1 += fast_exp2(fmaf(x[k + 1], kLog2e, neg));
+    }
+  }
+  st.s = st.s * fast_exp2(fmaf(st.m, kLog2e, neg)) + (acc0 + acc1);
+  st.m = m;
+}
+
+constexpr int kCeFwdCtasPerSM = 4;
+constexpr int kCeWarps = kCeThreads / 32;
+
+__device__ __forceinline__ MS warp_merge(MS st) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    MS other;
+    other.m = __shfl_xor_sync(0xffffffffu, st.m, o);
+    other.s = __shfl_xor_sync(0xffffffffu, st.s, o);
+    st = ms_merge(st, other);
+  }
+  return st;
+}
+
+// The unit of work is a WARP, not a CTA: warp w of the grid walks work items (row, part) with
+// stride (gridDim.x * 8). A warp streams its piece with 512-byte coalesced requests, merges with
+// shuffles only and never waits for another warp, so there is no CTA barrier on the data path
+// (an earlier CTA-per-row version spent as many issue slots stalled on bar.sync as on memory).
+// Loads for the next batch of packs are issued before the current batch is reduced.
 template <bool BF16>
-__global__ void __launch_bounds__(kCeThreads)
+__global__ void __launch_bounds__(kCeThreads, kCeFwdCtasPerSM)
 ce_forward_kernel(const typename Elem<BF16>::T* __restrict__ logits,
                   const long long* __restrict__ labels, long long n_rows, int vocab,
                   long long row_stride, long long ignore_index, int split,
@@ -149,61 +194,82 @@ ce_forward_kernel(const typename Elem<BF16>::T* __restrict__ logits,
   using T = typename E::T;
   constexpr int PP = E::kPerPack;
   constexpr int U = 4;
-  __shared__ MS s_ms[kCeThreads / 32];
-  __shared__ float s_f[kCeThreads / 32];
+  __shared__ float s_f[kCeWarps];
   __shared__ bool s_last;
 
   const CeScratch sc = carve(ws, n_rows);
-  const long long row = blockIdx.x / split;
-  const int part = (int)(blockIdx.x - row * split);
-  const T* zrow = logits + row * row_stride;
+  const long long items = n_rows * split;
+  const int lane = threadIdx.x & 31;
+  const long long warp0 = (long long)blockIdx.x * kCeWarps + (threadIdx.x >> 5);
+  const long long nwarps = (long long)gridDim.x * kCeWarps;
+  for (long long item = warp0; item < items; item += nwarps) {
+    const long long row = item / split;
+    const int part = (int)(item - row * split);
+    const T* zrow = logits + row * row_stride;
 
-  // Column range of this CTA, in whole packs when the row is 16-byte aligned.
-  const bool vec_ok = ((((uintptr_t)zrow) & 15) == 0);
-  const int npack = vec_ok ? vocab / PP : 0;
-  const int per = (npack + split - 1) / split;
-  const int p0 = min(part * per, npack), p1 = min(p0 + per, npack);
+    // Lane 0 fetches the label and the label's logit now; they are needed only after the
+    // piece has been streamed, so their latency hides behind the main loop.
+    long long y = ignore_index;
+    float zy = 0.f;
+    if (lane == 0 && part == 0) {
+      y = labels[row];
+      if (y != ignore_index && y >= 0 && y < vocab) zy = E::load1(zrow + y);
+    }
 
-  MS st{-INFINITY, 0.f};
-  const uint4* zp = reinterpret_cast<const uint4*>(zrow);
-  int i = p0 + threadIdx.x;
-  for (; i + (U - 1) * kCeThreads < p1; i += U * kCeThreads) {
-    uint4 r[U];
+    const bool vec_ok = ((((uintptr_t)zrow) & 15) == 0);
+    const int npack = vec_ok ? vocab / PP : 0;
+    const int per = (npack + split - 1) / split;
+    const int p0 = min(part * per, npack), p1 = min(p0 + per, npack);
+    const uint4* zp = reinterpret_cast<const uint4*>(zrow);
+
+    MS st{-INFINITY, 0.f};
+    int i = p0 + lane;
+    constexpr int STEP = U * 32;
+    if (i + (U - 1) * 32 < p1) {
+      uint4 cur[U];
 #pragma unroll
-    for (int u = 0; u < U; ++u) r[u] = ld_nc16(zp + i + u * kCeThreads);
-    float x[U * PP];
+      for (int u = 0; u < U; ++u) cur[u] = ld_nc16(zp + i + u * 32);
+      for (i += STEP; i + (U - 1) * 32 < p1; i += STEP) {
+        uint4 nxt[U];
 #pragma unroll
-    for (int u = 0; u < U; ++u) E::unpack(r[u], x + u * PP);
-    ms_update<U * PP>(st, x);
-  }
-  for (; i < p1; i += kCeThreads) {
-    float x[PP];
-    E::unpack(ld_nc16(zp + i), x);
-    ms_update<PP>(st, x);
-  }
-  // Scalar tail (vocab % PP, or the whole row if it is not 16-byte aligned): last part only.
-  if (part == split - 1) {
-    for (int j = npack * PP + threadIdx.x; j < vocab; j += kCeThreads) {
-      float x[1] = {E::load1(zrow + j)};
-      ms_update<1>(st, x);
+        for (int u = 0; u < U; ++u) nxt[u] = ld_nc16(zp + i + u * 32);
+        ms_update_packs<BF16, U>(st, cur);
+#pragma unroll
+        for (int u = 0; u < U; ++u) cur[u] = nxt[u];
+      }
+      ms_update_packs<BF16, U>(st, cur);
+    }
+    for (; i < p1; i += 32) {
+      const uint4 one[1] = {ld_nc16(zp + i)};
+      ms_update_packs<BF16, 1>(st, one);
+    }
+    // Scalar tail (vocab % PP, or the whole row if it is not 16-byte aligned): last part only.
+    if (part == split - 1) {
+      for (int j = npack * PP + lane; j < vocab; j += 32) {
+        float x[1] = {E::load1(zrow + j)};
+        ms_update<1>(st, x);
+      }
+    }
+    st = warp_merge(st);
+
+    if (lane == 0) {
+      if (split == 1) {
+        // Whole row seen by this warp: finish the row here so the last CTA only has to sum.
+        const float lse = st.m + logf(st.s);
+        row_lse[row] = lse;
+        float l = 0.f;
+        if (y != ignore_index)
+          l = (y < 0 || y >= vocab) ? __int_as_float(0x7fc00000)  // out-of-range label poisons the loss
+                                    : lse - zy;
+        sc.row_loss[row] = l;
+      } else {
+        sc.partial[row * split + part] = st;
+        if (part == 0) sc.row_loss[row] = zy;  // split rows: the slot carries z[y] to the fold below
+      }
     }
   }
-  st = block_merge(st, s_ms);
-
+  __syncthreads();  // every warp of this CTA has written its results
   if (threadIdx.x == 0) {
-    if (split == 1) {
-      // Whole row seen by this CTA: finish the row here so the last CTA only has to sum.
-      const float lse = st.m + logf(st.s);
-      row_lse[row] = lse;
-      const long long y = labels[row];
-      float l = 0.f;
-      if (y != ignore_index)
-        l = (y < 0 || y >= vocab) ? __int_as_float(0x7fc00000)  // out-of-range label poisons the loss
-                                  : lse - E::load1(zrow + y);
-      sc.row_loss[row] = l;
-    } else {
-      sc.partial[row * split + part] = st;
-    }
     __threadfence();
     const unsigned int arrived = atomicAdd(sc.counter, 1u);
     s_last = (arrived == gridDim.x - 1);
@@ -214,15 +280,13 @@ ce_forward_kernel(const typename Elem<BF16>::T* __restrict__ logits,
 
   // Last CTA to arrive: (split rows only) fold the partials of each row, then sum the valid
   // rows' losses in a fixed order (thread-strided, then a tree), so the result does not
-  // depend on which CTA happened to be last.
+  // depend on which CTA happened to be last. Everything read here is coalesced.
   float acc = 0.f, cnt = 0.f;
   for (long long r = threadIdx.x; r < n_rows; r += kCeThreads) {
     const long long y = labels[r];
     const bool valid = (y != ignore_index);
-    float l;
-    if (split == 1) {
-      l = __ldcg(sc.row_loss + r);
-    } else {
+    float l = __ldcg(sc.row_loss + r);
+    if (split != 1) {
       MS t{-INFINITY, 0.f};
       for (int k = 0; k < split; ++k) {
         const float2 q = __ldcg(reinterpret_cast<const float2*>(sc.partial + r * split + k));
@@ -230,10 +294,7 @@ ce_forward_kernel(const typename Elem<BF16>::T* __restrict__ logits,
       }
       const float lse = t.m + logf(t.s);
       row_lse[r] = lse;
-      l = 0.f;
-      if (valid)
-        l = (y < 0 || y >= vocab) ? __int_as_float(0x7fc00000)
-                                  : lse - E::load1(logits + r * row_stride + y);
+      l = (y < 0 || y >= vocab) ? __int_as_float(0x7fc00000) : lse - l;
     }
     if (valid) {
       acc += l;
@@ -249,74 +310,106 @@ ce_forward_kernel(const typename Elem<BF16>::T* __restrict__ logits,
   }
 }
 
+constexpr int kCeBwdCtasPerSM = 6;
+constexpr int kCeBwdU = 4;  // packs per thread per tile
+
+// Persistent over (row, tile) work items; a tile is kCeBwdU * 256 packs of one row.
 template <bool BF16>
-__global__ void __launch_bounds__(kCeThreads)
+__global__ void __launch_bounds__(kCeThreads, kCeBwdCtasPerSM)
 ce_backward_kernel(const typename Elem<BF16>::T* __restrict__ logits,
                    const long long* __restrict__ labels, const float* __restrict__ row_lse,
                    const float* __restrict__ grad_out, const float* __restrict__ nvalid,
-                   int vocab, long long row_stride, long long ignore_index, int tiles_per_row,
-                   typename Elem<BF16>::T* __restrict__ dlogits) {
+                   long long n_rows, int vocab, long long row_stride, long long ignore_index,
+                   int tiles_per_row, typename Elem<BF16>::T* __restrict__ dlogits) {
   using E = Elem<BF16>;
   using T = typename E::T;
   constexpr int PP = E::kPerPack;
-  constexpr int U = 4;
-  const long long row = blockIdx.x / tiles_per_row;
-  const int tile = (int)(blockIdx.x - row * tiles_per_row);
-  const T* zrow = logits + row * row_stride;
-  T* drow = dlogits + row * row_stride;
-  const long long y = labels[row];
-  const bool valid = (y != ignore_index);
-  const float coef = valid ? __ldg(grad_out) / __ldg(nvalid) : 0.f;
-  const float lse = __ldg(row_lse + row);
+  constexpr int U = kCeBwdU;
+  const float scale = __ldg(grad_out) / __ldg(nvalid);
+  const long long items = n_rows * tiles_per_row;
+  for (long long item = blockIdx.x; item < items; item += gridDim.x) {
+    const long long row = item / tiles_per_row;
+    const int tile = (int)(item - row * tiles_per_row);
+    const T* zrow = logits + row * row_stride;
+    T* drow = dlogits + row * row_stride;
+    const long long y = __ldg(labels + row);
+    const bool valid = (y != ignore_index);
+    const float coef = valid ? scale : 0.f;
+    const float neg = -__ldg(row_lse + row) * kLog2e;
 
-  const bool vec_ok = (((((uintptr_t)zrow) | ((uintptr_t)drow)) & 15) == 0);
-  const int npack = vec_ok ? vocab / PP : 0;
-  const int per = U * kCeThreads;
-  const int p0 = min(tile * per, npack), p1 = min(p0 + per, npack);
-  const uint4* zp = reinterpret_cast<const uint4*>(zrow);
-  uint4* dp = reinterpret_cast<uint4*>(drow);
+    const bool vec_ok = (((((uintptr_t)zrow) | ((uintptr_t)drow)) & 15) == 0);
+    const int npack = vec_ok ? vocab / PP : 0;
+    const int per = U * kCeThreads;
+    const int p0 = min(tile * per, npack), p1 = min(p0 + per, npack);
+    const uint4* zp = reinterpret_cast<const uint4*>(zrow);
+    uint4* dp = reinterpret_cast<uint4*>(drow);
 
-  if (!valid) {
-    const uint4 zero = make_uint4(0, 0, 0, 0);
-    for (int i = p0 + threadIdx.x; i < p1; i += kCeThreads) dp[i] = zero;
-  } else {
-    uint4 r[U];
+    if (!valid) {
+      const uint4 zero = make_uint4(0, 0, 0, 0);
+      for (int i = p0 + threadIdx.x; i < p1; i += kCeThreads) dp[i] = zero;
+    } else {
+      uint4 r[U];
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int i = p0 + threadIdx.x + u * kCeThreads;
-      if (i < p1) r[u] = ld_nc16(zp + i);
-    }
+      for (int u = 0; u < U; ++u) {
+        const int i = p0 + threadIdx.x + u * kCeThreads;
+        if (i < p1) r[u] = ld_nc16(zp + i);
+      }
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int i = p0 + threadIdx.x + u * kCeThreads;
-      if (i < p1) {
-        float x[PP];
-        E::unpack(r[u], x);
-        const int col0 = i * PP;
+      for (int u = 0; u < U; ++u) {
+        const int i = p0 + threadIdx.x + u * kCeThreads;
+        if (i < p1) {
+          float x[PP];
+          E::unpack(r[u], x);
 #pragma unroll
-        for (int k = 0; k < PP; ++k) {
-          const float p = fast_exp2((x[k] - lse) * kLog2e);
-          x[k] = (p - ((long long)(col0 + k) == y ? 1.f : 0.f)) * coef;
+          for (int k = 0; k < PP; ++k) x[k] = fast_exp2(fmaf(x[k], kLog2e, neg)) * coef;
+          dp[i] = E::pack(x);
         }
-        dp[i] = E::pack(x);
+      }
+      // The label's column lies in exactly one pack of one thread of one tile. That thread
+      // overwrites the element after its vector store (same thread, same address: program
+      // order holds), which keeps the main loop free of per-column compares.
+      asm volatile("" ::: "memory");  // keep the compiler from moving the patch above the stores
+      const long long yp = y / PP;
+      if (y >= 0 && y < (long long)npack * PP && yp >= p0 && yp < p1 &&
+          (int)((yp - p0) % kCeThreads) == (int)threadIdx.x) {
+        const float p = fast_exp2(fmaf(E::load1(zrow + y), kLog2e, neg));
+        E::store1(drow + y, (p - 1.f) * coef);
       }
     }
-  }
-  if (tile == tiles_per_row - 1) {
-    for (int j = npack * PP + threadIdx.x; j < vocab; j += kCeThreads) {
-      float o = 0.f;
-      if (valid) {
-        const float p = fast_exp2((E::load1(zrow + j) - lse) * kLog2e);
-        o = (p - ((long long)j == y ? 1.f : 0.f)) * coef;
+    if (tile == tiles_per_row - 1) {
+      for (int j = npack * PP + threadIdx.x; j < vocab; j += kCeThreads) {
+        float o = 0.f;
+        if (valid) {
+          const float p = fast_exp2(fmaf(E::load1(zrow + j), kLog2e, neg));
+          o = (p - ((long long)j == y ? 1.f : 0.f)) * coef;
+        }
+        E::store1(drow + j, o);
       }
-      E::store1(drow + j, o);
     }
   }
 }
 
+// CTAs per SM the persistent grids are capped at; 0 = one CTA per work item (no cap).
+// B2_CE_FWD_CTAS_PER_SM / B2_CE_BWD_CTAS_PER_SM override the defaults for tuning runs.
+static int env_int(const char* name, int dflt) {
+  const char* v = std::getenv(name);
+  return (v && *v) ? std::atoi(v) : dflt;
+}
+static long long fwd_grid(long long items) {  // items are per-warp work units, 8 warps per CTA
+  static const int cap = env_int("B2_CE_FWD_CTAS_PER_SM", 0);
+  const long long ctas = (items + kCeWarps - 1) / kCeWarps;
+  return cap > 0 ? std::min<long long>(ctas, (long long)kNumSMs * cap) : ctas;
+}
+static long long bwd_grid(long long items) {
+  static const int cap = env_int("B2_CE_BWD_CTAS_PER_SM", 0);
+  return cap > 0 ? std::min<long long>(items, (long long)kNumSMs * cap) : items;
+}
+
 static int pick_split(long long n_rows) {
-  // Split a row over several CTAs only while one CTA per row cannot fill the chip.
-  const long long target = (long long)kNumSMs * 4;
+  // A row is split over several warps only while one warp per row cannot fill the chip twice
+  // over (148 SMs x 32 resident warps): small batches are latency-bound, and shorter pieces
+  // mean fewer dependent load rounds per warp.
+  const long long target = 2ll * kNumSMs * kCeFwdCtasPerSM * kCeWarps;
   int s = 1;
   while (s < kCeMaxSplit && n_rows * s < target) s <<= 1;
   return s;
@@ -350,13 +443,13 @@ extern "C" int b2_ce_forward(const void* logits, const int64_t* labels, int64_t 
     return B2_OK;
   }
   B2_REQUIRE(logits && labels && row_lse && workspace, "ce_forward: null pointer");
+  B2_REQUIRE(n_rows * kCeMaxSplit < (1ll << 31), "ce_forward: too many rows");
   B2_REQUIRE(workspace_bytes >= b2_ce_workspace_bytes(n_rows, vocab),
              "ce_forward: workspace %zu B < required %zu B", workspace_bytes,
              b2_ce_workspace_bytes(n_rows, vocab));
   B2_REQUIRE((((uintptr_t)workspace) & 15) == 0, "ce_forward: workspace must be 16-byte aligned");
   const int split = pick_split(n_rows);
-  const long long grid = n_rows * split;
-  B2_REQUIRE(grid < (1ll << 31), "ce_forward: too many rows");
+  const long long grid = fwd_grid(n_rows * split);
   if (dtype == B2_BF16) {
     ce_forward_kernel<true><<<(unsigned)grid, kCeThreads, 0, (cudaStream_t)stream>>>(
         (const __nv_bfloat16*)logits, (const long long*)labels, n_rows, (int)vocab, row_stride,
@@ -383,19 +476,19 @@ extern "C" int b2_ce_backward(const void* logits, const int64_t* labels, const f
   B2_REQUIRE(logits && labels && row_lse && grad_out && nvalid && dlogits, "ce_backward: null pointer");
   const int pp = dtype == B2_BF16 ? 8 : 4;
   const long long npack = vocab / pp;
-  const int per = 4 * kCeThreads;
+  const int per = kCeBwdU * kCeThreads;
   long long tiles = (npack + per - 1) / per;
   if (tiles < 1) tiles = 1;
-  const long long grid = n_rows * tiles;
-  B2_REQUIRE(grid < (1ll << 31), "ce_backward: too many tiles");
+  B2_REQUIRE(n_rows * tiles < (1ll << 31), "ce_backward: too many tiles");
+  const long long grid = bwd_grid(n_rows * tiles);
   if (dtype == B2_BF16) {
     ce_backward_kernel<true><<<(unsigned)grid, kCeThreads, 0, (cudaStream_t)stream>>>(
-        (const __nv_bfloat16*)logits, (const long long*)labels, row_lse, grad_out, nvalid,
+        (const __nv_bfloat16*)logits, (const long long*)labels, row_lse, grad_out, nvalid, n_rows,
         (int)vocab, row_stride, ignore_index, (int)tiles, (__nv_bfloat16*)dlogits);
   } else {
     ce_backward_kernel<false><<<(unsigned)grid, kCeThreads, 0, (cudaStream_t)stream>>>(
-        (const float*)logits, (const long long*)labels, row_lse, grad_out, nvalid, (int)vocab,
-        row_stride, ignore_index, (int)tiles, (float*)dlogits);
+        (const float*)logits, (const long long*)labels, row_lse, grad_out, nvalid, n_rows,
+        (int)vocab, row_stride, ignore_index, (int)tiles, (float*)dlogits);
   }
   B2_CUDA_CHECK(cudaGetLastError());
   return B2_OK;
@@ -482,7 +575,7 @@ extern "C" int b2_ce_forward_noalloc(const void* logits, const int64_t* labels, 
   // The array still holds the previous call's contents; only the counter has to be zero.
   B2_CUDA_CHECK(cudaMemsetAsync(ws, 0, 16, st));
   const int split = pick_split(n_rows);
-  const long long grid = n_rows * split;
+  const long long grid = fwd_grid(n_rows * split);
   if (dtype == B2_BF16) {
     ce_forward_kernel<true><<<(unsigned)grid, kCeThreads, 0, st>>>(
         (const __nv_bfloat16*)logits, (const long long*)labels, n_rows, (int)vocab, row_stride,

@@ -59,12 +59,10 @@ class AdamW(Optimizer):
                         fused=None, decoupled_weight_decay=True)
         super().__init__(params, defaults)
         self._lib = _lib.load()
-        self._table_key: Optional[tuple] = None
+        self._plan: Optional["_Plan"] = None
         self._table_dev: Optional[torch.Tensor] = None
         self._table_pinned: Optional[torch.Tensor] = None
         self._table_event: Optional[torch.cuda.Event] = None
-        self._n_tensors = 0
-        self._total_chunks = 0
         #: optional device fp32 scalar multiplied into every gradient inside the kernel
         #: (gradient-clipping fold-in); set by clip helpers, cleared after each step.
         self.grad_scale: Optional[torch.Tensor] = None
@@ -74,81 +72,104 @@ class AdamW(Optimizer):
 
     def __setstate__(self, state: dict[str, Any]) -> None:
         super().__setstate__(state)
+        self.__dict__.setdefault("_plan", None)
+        self.__dict__.setdefault("grad_scale", None)
+        self.__dict__.setdefault("kernel_events", None)
         for group in self.param_groups:
             group.setdefault("amsgrad", False)
             group.setdefault("maximize", False)
             group.setdefault("decoupled_weight_decay", True)
 
-    # -- table ---------------------------------------------------------------------
-    def _gather(self):
-        """Params with grads, lazily initialised state, and one hyper set per (group, step)."""
-        rows = []          # (p, g, m, v, numel, hyper_idx)
-        hypers: list[tuple] = []
-        hyper_index: dict[tuple, int] = {}
-        device = None
-        for group in self.param_groups:
-            beta1, beta2 = group["betas"]
-            lr = group["lr"]
-            if isinstance(lr, torch.Tensor):
-                lr = float(lr)
-            for p in group["params"]:
-                g = p.grad
-                if g is None:
-                    continue
-                if g.is_sparse:
-                    raise RuntimeError("AdamW does not support sparse gradients")
-                if not p.is_cuda:
-                    raise RuntimeError("b200 AdamW has no CPU path: parameter is on " + str(p.device))
-                if p.dtype != torch.float32 or g.dtype != torch.float32:
-                    raise NotImplementedError(
-                        f"b200 AdamW: fp32 params and grads only (got {p.dtype} / {g.dtype}); "
-                        "AMP keeps fp32 master params, which is what the reference scripts train")
-                if not p.is_contiguous():
-                    raise NotImplementedError("b200 AdamW: non-contiguous parameter")
-                if device is None:
-                    device = p.device
-                elif p.device != device:
-                    raise NotImplementedError("b200 AdamW: parameters on more than one device")
-                if not g.is_contiguous():
-                    g = g.contiguous()
-                    p.grad = g
-                state = self.state[p]
-                if len(state) == 0:  # adam.py:162-190
-                    state["step"] = torch.tensor(0.0, dtype=torch.float32)
-                    state["exp_avg"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
-                    state["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
-                state["step"] += 1
-                step = int(state["step"].item()) if state["step"].device.type == "cpu" else int(state["step"])
-                key = (lr, beta1, beta2, group["eps"], group["weight_decay"], step)
-                idx = hyper_index.get(key)
-                if idx is None:
-                    idx = hyper_index[key] = len(hypers)
-                    hypers.append(key)
-                rows.append((p.data_ptr(), g.data_ptr(), state["exp_avg"].data_ptr(),
-                             state["exp_avg_sq"].data_ptr(), p.numel(), idx))
-        return rows, hypers, device
+    # -- plan: everything about a step that does not change from one step to the next -----
+    def add_param_group(self, param_group: dict[str, Any]) -> None:
+        super().add_param_group(param_group)
+        self._plan = None
 
-    def _upload_table(self, rows, device) -> None:
-        n = len(rows)
+    def load_state_dict(self, state_dict: dict[str, Any]) -> None:
+        super().load_state_dict(state_dict)
+        self._plan = None
+
+    @staticmethod
+    def _check_grad(p: torch.Tensor, g: torch.Tensor) -> None:
+        if g.is_sparse:
+            raise RuntimeError("AdamW does not support sparse gradients")
+        if g.dtype != torch.float32:
+            raise NotImplementedError(f"b200 AdamW: fp32 gradients only (got {g.dtype})")
+        if g.device != p.device:
+            raise RuntimeError("b200 AdamW: gradient and parameter are on different devices")
+
+    def _rebuild_plan(self, all_params, grads, pattern):
+        """Slow path: validate every tensor, create missing state (adam.py:162-190), build the
+        host table. Runs at the first step and whenever the set of params with grads changes."""
+        live, group_of, device = [], [], None
+        gi_of = {}
+        for gi, group in enumerate(self.param_groups):
+            for p in group["params"]:
+                gi_of[id(p)] = gi
+        for p, g in zip(all_params, grads):
+            if g is None:
+                continue
+            if not p.is_cuda:
+                raise RuntimeError("b200 AdamW has no CPU path: parameter is on " + str(p.device))
+            if p.dtype != torch.float32:
+                raise NotImplementedError(
+                    f"b200 AdamW: fp32 parameters only (got {p.dtype}); AMP keeps fp32 master "
+                    "params, which is what the reference scripts train")
+            if not p.is_contiguous():
+                raise NotImplementedError("b200 AdamW: non-contiguous parameter")
+            if device is None:
+                device = p.device
+            elif p.device != device:
+                raise NotImplementedError("b200 AdamW: parameters on more than one device")
+            self._check_grad(p, g)
+            state = self.state[p]
+            if len(state) == 0:
+                state["step"] = torch.tensor(0.0, dtype=torch.float32)
+                state["exp_avg"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
+                state["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
+            live.append(p)
+            group_of.append(gi_of[id(p)])
+        plan = _Plan()
+        plan.pattern, plan.params, plan.device = pattern, live, device
+        n = len(live)
+        plan.group_of = np.asarray(group_of, dtype=np.int64)
+        plan.step_tensors = [self.state[p]["step"] for p in live]
+        plan.steps = np.asarray([int(float(t)) for t in plan.step_tensors], dtype=np.int64)
         host = np.zeros(n, dtype=_TABLE_DTYPE)
-        arr = np.asarray(rows, dtype=np.int64)
-        host["p"], host["g"], host["m"], host["v"] = (arr[:, 0].astype(np.uint64), arr[:, 1].astype(np.uint64),
-                                                      arr[:, 2].astype(np.uint64), arr[:, 3].astype(np.uint64))
-        host["numel"], host["hyper"] = arr[:, 4], arr[:, 5].astype(np.int32)
-        total = self._lib.b2_adamw_plan(host.ctypes.data_as(C.POINTER(_lib.AdamWTensor)), n)
+        host["p"] = [p.data_ptr() for p in live]
+        host["m"] = [self.state[p]["exp_avg"].data_ptr() for p in live]
+        host["v"] = [self.state[p]["exp_avg_sq"].data_ptr() for p in live]
+        host["numel"] = [p.numel() for p in live]
+        # one hyper class per distinct (group, step); all members advance together afterwards
+        keys = plan.group_of * (1 << 40) + plan.steps
+        uniq, inverse = np.unique(keys, return_inverse=True)
+        if len(uniq) > _lib.B2_ADAMW_MAX_HYPERS:
+            raise NotImplementedError(
+                f"b200 AdamW: {len(uniq)} distinct (group, step) hyper sets in one step; "
+                f"the kernel takes {_lib.B2_ADAMW_MAX_HYPERS}")
+        host["hyper"] = inverse.astype(np.int32)
+        plan.class_group = (uniq >> 40).astype(np.int64)
+        plan.class_step = (uniq & ((1 << 40) - 1)).astype(np.int64)
+        total = self._lib.b2_adamw_plan(host.ctypes.data_as(C.POINTER(_lib.AdamWTensor)), n) if n else 0
         if total < 0:
             _lib.check(int(total))
+        plan.host, plan.total_chunks, plan.n = host, int(total), n
+        plan.dirty = True
+        return plan
+
+    def _upload_table(self, plan) -> None:
+        host = plan.host
         nbytes = host.nbytes
         if self._table_pinned is None or self._table_pinned.numel() < nbytes:
             self._table_pinned = torch.empty(max(nbytes, 4096), dtype=torch.uint8, pin_memory=True)
-            self._table_dev = torch.empty(max(nbytes, 4096), dtype=torch.uint8, device=device)
+            self._table_dev = torch.empty(max(nbytes, 4096), dtype=torch.uint8, device=plan.device)
             self._table_event = torch.cuda.Event()
         else:
             self._table_event.synchronize()  # previous async upload has consumed the pinned buffer
         self._table_pinned[:nbytes].copy_(torch.from_numpy(host.view(np.uint8)))
         self._table_dev[:nbytes].copy_(self._table_pinned[:nbytes], non_blocking=True)
         self._table_event.record()
-        self._n_tensors, self._total_chunks = n, int(total)
+        plan.dirty = False
 
     # -- step ----------------------------------------------------------------------
     @torch.no_grad()
@@ -157,21 +178,49 @@ class AdamW(Optimizer):
         if closure is not None:
             with torch.enable_grad():
                 loss = closure()
-        rows, hypers, device = self._gather()
-        if not rows:
+        all_params = [p for group in self.param_groups for p in group["params"]]
+        grads = [p.grad for p in all_params]
+        pattern = [g is not None for g in grads]
+        plan = self._plan
+        if plan is None or plan.pattern != pattern:
+            plan = self._plan = self._rebuild_plan(all_params, grads, pattern)
+        n = plan.n
+        if n == 0:
             return loss
-        if len(hypers) > _lib.B2_ADAMW_MAX_HYPERS:
-            raise NotImplementedError(
-                f"b200 AdamW: {len(hypers)} distinct (group, step) hyper sets in one step; "
-                f"the kernel takes {_lib.B2_ADAMW_MAX_HYPERS}")
-        key = tuple(rows)
+        live = plan.params
+        live_grads = [g for g in grads if g is not None]
+        gptrs = np.fromiter((g.data_ptr() for g in live_grads), dtype=np.uint64, count=n)
+        pptrs = np.fromiter((p.data_ptr() for p in live), dtype=np.uint64, count=n)
+        host = plan.host
+        changed = np.nonzero(gptrs != host["g"])[0]
+        if changed.size:
+            for i in changed:  # new gradient tensors: re-validate just those
+                g = live_grads[i]
+                self._check_grad(live[i], g)
+                if not g.is_contiguous():
+                    g = live[i].grad = g.contiguous()
+                    gptrs[i] = g.data_ptr()
+            host["g"] = gptrs
+            plan.dirty = True
+        if not np.array_equal(pptrs, host["p"]):  # p.data was re-homed (e.g. module.to(...))
+            plan = self._plan = self._rebuild_plan(all_params, grads, pattern)
+            plan.host["g"] = gptrs
+            host = plan.host
+        # state["step"] += 1 for every live param, in one call; python mirror for the scalars
+        torch._foreach_add_(plan.step_tensors, 1)
+        plan.steps += 1
+        plan.class_step += 1
+        n_h = len(plan.class_group)
+        hp = (_lib.AdamWHyper * n_h)()
+        for i in range(n_h):
+            group = self.param_groups[int(plan.class_group[i])]
+            lr = group["lr"]
+            hp[i] = _lib.AdamWHyper(float(lr), group["betas"][0], group["betas"][1], group["eps"],
+                                    group["weight_decay"], int(plan.class_step[i]))
+        device = plan.device
         with torch.cuda.device(device):
-            if key != self._table_key:
-                self._upload_table(rows, device)
-                self._table_key = key
-            hp = (_lib.AdamWHyper * len(hypers))()
-            for i, (lr, b1, b2, eps, wd, step) in enumerate(hypers):
-                hp[i] = _lib.AdamWHyper(lr, b1, b2, eps, wd, step)
+            if plan.dirty:
+                self._upload_table(plan)
             gs = self.grad_scale
             if gs is not None and (gs.dtype != torch.float32 or gs.device != device or gs.numel() != 1):
                 raise ValueError("grad_scale must be a 1-element fp32 tensor on the parameters' device")
@@ -180,7 +229,7 @@ class AdamW(Optimizer):
                 ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
                 ev[0].record()
             _lib.check(self._lib.b2_adamw_step(
-                self._table_dev.data_ptr(), self._n_tensors, self._total_chunks, hp, len(hypers),
+                self._table_dev.data_ptr(), n, plan.total_chunks, hp, n_h,
                 gs.data_ptr() if gs is not None else None,
                 torch.cuda.current_stream(device).cuda_stream))
             _lib.count_launch()
@@ -189,3 +238,10 @@ class AdamW(Optimizer):
                 self.kernel_events.append(ev)
         self.grad_scale = None
         return loss
+
+
+class _Plan:
+    """Cached per-optimizer launch plan (see AdamW._rebuild_plan)."""
+
+    __slots__ = ("pattern", "params", "device", "group_of", "step_tensors", "steps", "host", "class_group",
+                 "class_step", "total_chunks", "n", "dirty")
