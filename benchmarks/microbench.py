@@ -262,6 +262,11 @@ def bench_allreduce(args):
                     continue
                 ms = timed(lambda: comm.allreduce_(x, 1.0 / world, wire=wire, algo=algo), iters, args.warmup)
                 rows.append((f"b200_{wire}_{algo}", ms))
+        if world > 1:
+            reg = comm.register(x)
+            rows.append(("b200_fp32_zero_copy_inplace",
+                         timed(lambda: comm.allreduce_registered_(reg, x, 1.0 / world), iters, args.warmup)))
+            comm.unregister(reg)
         if world > 1 and args.only != "ours":
             def nccl():
                 x.div_(world)

@@ -9,7 +9,7 @@ from pathlib import Path
 from .build import LIB_PATH, build
 
 B2_F32, B2_BF16 = 0, 1
-B2_ALGO_AUTO, B2_ALGO_ONE_SHOT, B2_ALGO_TWO_SHOT = 0, 1, 2
+B2_ALGO_AUTO, B2_ALGO_ONE_SHOT, B2_ALGO_TWO_SHOT, B2_ALGO_TWO_SHOT_INPLACE = 0, 1, 2, 3
 B2_IPC_HANDLE_BYTES = 64
 B2_MAX_WORLD = 8
 B2_ADAMW_MAX_HYPERS = 16
@@ -54,6 +54,10 @@ SIGNATURES = {
     "b2_comm_open_peers": (C.c_int, [_vp, _vp]),
     "b2_comm_max_numel": (_i64, [_vp, _i32]),
     "b2_allreduce": (C.c_int, [_vp, _vp, _i64, _i32, _f32, _i32, _vp]),
+    "b2_comm_export": (C.c_int, [_vp, _vp, _vp, C.POINTER(C.c_uint64)]),
+    "b2_comm_register": (C.c_int, [_vp, _vp, _sz, _vp, C.POINTER(C.c_uint64), C.POINTER(C.c_int)]),
+    "b2_comm_unregister": (C.c_int, [_vp, _i32]),
+    "b2_allreduce_registered": (C.c_int, [_vp, _i32, _i64, _f32, _vp]),
     "b2_comm_status": (C.c_int, [_vp]),
     "b2_comm_destroy": (C.c_int, [_vp]),
     "b2_allreduce_emulated_scratch_bytes": (_sz, [_i32, _i64]),

@@ -91,6 +91,45 @@ class P2PComm:
         _lib.count_launch(max(1, -(-tensor.numel() // max(cap, 1))))
         return tensor
 
+    # -- zero-copy path: buffers that live across steps, mapped by every peer ----------------
+    def register(self, tensor: torch.Tensor, peers: Optional[list] = None) -> int:
+        """Collective (unless ``peers`` is given): export the allocation holding ``tensor``,
+        all-gather (handle, offset) and map every peer's buffer. Returns a registration id for
+        ``allreduce_registered_``. The tensor's memory must stay allocated until ``unregister``."""
+        if tensor.device != self.device or tensor.dtype != torch.float32 or not tensor.is_contiguous():
+            raise ValueError("register: contiguous fp32 tensor on the communicator's device required")
+        mine = self.export(tensor)
+        if peers is None:
+            peers = [None] * self.world
+            if self.world > 1:
+                dist.all_gather_object(peers, mine, group=self.group)
+            else:
+                peers = [mine]
+        handles = b"".join(p[0] for p in peers)
+        offsets = (C.c_uint64 * self.world)(*[p[1] for p in peers])
+        reg = C.c_int(-1)
+        _lib.check(self._lib.b2_comm_register(self._ctx, tensor.data_ptr(), tensor.numel() * 4, handles, offsets,
+                                              C.byref(reg)))
+        return reg.value
+
+    def export(self, tensor: torch.Tensor) -> tuple:
+        """(64-byte IPC handle of the allocation containing ``tensor``, byte offset inside it)."""
+        raw = C.create_string_buffer(_lib.B2_IPC_HANDLE_BYTES)
+        off = C.c_uint64(0)
+        _lib.check(self._lib.b2_comm_export(self._ctx, tensor.data_ptr(), raw, C.byref(off)))
+        return (raw.raw, off.value)
+
+    def unregister(self, reg_id: int) -> None:
+        _lib.check(self._lib.b2_comm_unregister(self._ctx, reg_id))
+
+    def allreduce_registered_(self, reg_id: int, tensor: torch.Tensor, scale: float = 1.0, *,
+                              stream: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
+        """In-place two-shot directly on the registered buffers (no staging copy)."""
+        s = (stream or torch.cuda.current_stream(self.device)).cuda_stream
+        _lib.check(self._lib.b2_allreduce_registered(self._ctx, reg_id, tensor.numel(), float(scale), s))
+        _lib.count_launch()
+        return tensor
+
     def check(self) -> None:
         """Synchronising health check: raises if a kernel timed out waiting for a peer."""
         _lib.check(self._lib.b2_comm_status(self._ctx))
@@ -130,10 +169,49 @@ class HookState:
     """State object handed to ``ddp.register_comm_hook``: the communicator plus the side stream
     the reductions run on, so they overlap the rest of backward like the Reducer's NCCL stream."""
 
-    def __init__(self, comm: Optional[P2PComm] = None, **comm_kwargs):
+    def __init__(self, comm: Optional[P2PComm] = None, zero_copy: Optional[bool] = None,
+                 zero_copy_min_bytes: Optional[int] = None, **comm_kwargs):
         self.comm = comm or default_comm(**comm_kwargs)
         self.stream = torch.cuda.Stream(device=self.comm.device)
         self.buckets_reduced = 0
+        # Zero-copy: once a bucket has shown up twice at the same address on EVERY rank (the
+        # Reducer's buckets are stable after its one rebuild), it is registered for peer access
+        # and reduced in place. Small buckets stay on the one-barrier staging path.
+        if zero_copy is None:
+            zero_copy = os.environ.get("B2_AR_ZERO_COPY", "1") != "0"
+        if zero_copy_min_bytes is None:
+            zero_copy_min_bytes = int(os.environ.get("B2_AR_ZERO_COPY_MIN_BYTES", str(4 << 20)))
+        self.zero_copy = bool(zero_copy) and self.comm.world > 1 and self.comm.wire == "fp32"
+        self.zero_copy_min_bytes = zero_copy_min_bytes
+        self._last_seen: dict[int, tuple] = {}    # bucket index -> (data_ptr, numel) at its last call
+        self._registered: dict[int, tuple] = {}   # bucket index -> (data_ptr, numel, reg_id)
+
+    def registration_for(self, index: int, buf: torch.Tensor) -> Optional[int]:
+        """Collective while the bucket is unregistered: every rank contributes (stable?, handle,
+        offset); the bucket is registered only if it is stable everywhere."""
+        key = (buf.data_ptr(), buf.numel())
+        reg = self._registered.get(index)
+        if reg is not None:
+            if reg[:2] != key:
+                raise RuntimeError(
+                    f"DDP bucket {index} moved after it was registered for peer access "
+                    f"({reg[:2]} -> {key}); rebuild the HookState (or set B2_AR_ZERO_COPY=0)")
+            return reg[2]
+        if not self.zero_copy or buf.numel() * 4 < self.zero_copy_min_bytes:
+            return None
+        stable = self._last_seen.get(index) == key
+        self._last_seen[index] = key
+        try:
+            mine = (stable,) + self.comm.export(buf)
+        except _lib.B2Error:
+            mine = (False, b"", 0)  # memory that cannot be exported (e.g. expandable segments)
+        votes: list = [None] * self.comm.world
+        dist.all_gather_object(votes, mine, group=self.comm.group)
+        if not all(v[0] for v in votes):
+            return None
+        reg_id = self.comm.register(buf, peers=[(v[1], v[2]) for v in votes])
+        self._registered[index] = key + (reg_id,)
+        return reg_id
 
 
 def p2p_allreduce_hook(state: HookState, bucket: dist.GradBucket) -> torch.futures.Future[torch.Tensor]:
@@ -149,8 +227,12 @@ def p2p_allreduce_hook(state: HookState, bucket: dist.GradBucket) -> torch.futur
     buf = bucket.buffer()
     producer = torch.cuda.current_stream(comm.device)
     state.stream.wait_stream(producer)
+    reg = state.registration_for(bucket.index(), buf) if state.zero_copy else None
     with torch.cuda.stream(state.stream):
-        comm.allreduce_(buf, 1.0 / comm.world, stream=state.stream)
+        if reg is not None:
+            comm.allreduce_registered_(reg, buf, 1.0 / comm.world, stream=state.stream)
+        else:
+            comm.allreduce_(buf, 1.0 / comm.world, stream=state.stream)
         buf.record_stream(state.stream)
         fut: torch.futures.Future[torch.Tensor] = torch.futures.Future(devices=[comm.device])
         fut.set_result(buf)

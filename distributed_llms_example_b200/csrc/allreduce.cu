@@ -25,6 +25,7 @@
 // Calls on one b2_comm must therefore be stream-ordered on every rank.
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 
 #include "common.cuh"
 
@@ -298,6 +299,108 @@ allreduce_kernel(const __grid_constant__ ArArgs<NV> args, long long numel, float
   }
 }
 
+
+// ---- zero-copy variant: buckets registered for peer access -------------------------------
+//
+// When the bucket itself is mapped by every peer (b2_comm_register), the staging copy
+// disappears: two-shot runs IN PLACE on the buckets.
+//   barrier A   every rank's bucket holds its local gradients (its producers are done)
+//   stage 1     rank r: slice r <- sum_k scale * bucket_k[slice r], rank order, written into
+//               its OWN bucket (only rank r ever reads slice r of rank r's bucket in stage 1)
+//   barrier B   every slice owner has published its reduced slice
+//   stage 2     rank r pulls reduced slice k from bucket_k for k != r into its own bucket
+//               (the CTA of rank k that read this sub-range in stage 1 is past barrier B)
+//   barrier C   nobody is still reading this rank's reduced slice when the kernel returns and
+//               the next backward starts overwriting the bucket
+// stage[k] of the RankView holds bucket_k as mapped by this rank; buf is bucket_rank.
+template <int W, int NV>
+__global__ void __launch_bounds__(kArThreads, 1)
+allreduce_inplace_kernel(const __grid_constant__ ArArgs<NV> args, long long numel, float scale,
+                         uint32_t epoch, unsigned long long timeout_ns) {
+  const RankView& v = args.v[NV == 1 ? 0 : blockIdx.y];
+  const int rank = v.rank;
+  const int nb = gridDim.x, b = blockIdx.x, tid = threadIdx.x;
+  const long long npack = numel / 4;
+  const long long tail0 = npack * 4;
+  float* __restrict__ buf = v.buf;
+  const long long Q = (npack + W - 1) / W;
+  const long long q = (Q + nb - 1) / nb;
+  constexpr int U = (W >= 8) ? 2 : 4;
+
+  cross_barrier<W>(v, epoch, timeout_ns);
+  {
+    const long long slo = min((long long)rank * Q, npack), shi = min(slo + Q, npack);
+    const long long lo = min(slo + (long long)b * q, shi), hi = min(lo + q, shi);
+    long long i = lo + tid;
+    for (; i + (U - 1) * kArThreads < hi; i += U * kArThreads) {
+      uint4 r[U][W];
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+#pragma unroll
+        for (int k = 0; k < W; ++k) r[u][k] = ld_peer16(v.stage[k] + (i + u * kArThreads) * 16);
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        float acc[4];
+#pragma unroll
+        for (int k = 0; k < W; ++k) {
+          float x[4];
+          Wire<false>::to_f(r[u][k], x);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float t = __fmul_rn(x[e], scale);
+            acc[e] = (k == 0) ? t : __fadd_rn(acc[e], t);
+          }
+        }
+        *reinterpret_cast<uint4*>(buf + (i + u * kArThreads) * 4) = Wire<false>::from_f(acc);
+      }
+    }
+    for (; i < hi; i += kArThreads) {
+      float acc[4];
+#pragma unroll
+      for (int k = 0; k < W; ++k) {
+        float x[4];
+        Wire<false>::to_f(ld_peer16(v.stage[k] + i * 16), x);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float t = __fmul_rn(x[e], scale);
+          acc[e] = (k == 0) ? t : __fadd_rn(acc[e], t);
+        }
+      }
+      *reinterpret_cast<uint4*>(buf + i * 4) = Wire<false>::from_f(acc);
+    }
+  }
+  // tail (numel % 4): every rank sums it redundantly now, writes it after barrier B
+  float tail_acc = 0.f;
+  const bool has_tail = (b == 0 && tid < numel - tail0);
+  if (has_tail) {
+#pragma unroll
+    for (int k = 0; k < W; ++k) {
+      const float t = __fmul_rn(Wire<false>::tail_load(v.stage[k] + tail0 * 4, tid), scale);
+      tail_acc = (k == 0) ? t : __fadd_rn(tail_acc, t);
+    }
+  }
+  cross_barrier<W>(v, epoch + 1, timeout_ns);
+  if (has_tail) buf[tail0 + tid] = tail_acc;
+  constexpr int U2 = 4;
+#pragma unroll 1
+  for (int k = 1; k < W; ++k) {
+    const int s = (rank + k) % W;
+    const char* src = v.stage[s];
+    const long long slo = min((long long)s * Q, npack), shi = min(slo + Q, npack);
+    const long long lo = min(slo + (long long)b * q, shi), hi = min(lo + q, shi);
+    long long i = lo + tid;
+    for (; i + (U2 - 1) * kArThreads < hi; i += U2 * kArThreads) {
+      uint4 r[U2];
+#pragma unroll
+      for (int u = 0; u < U2; ++u) r[u] = ld_peer16(src + (i + u * kArThreads) * 16);
+#pragma unroll
+      for (int u = 0; u < U2; ++u) *reinterpret_cast<uint4*>(buf + (i + u * kArThreads) * 4) = r[u];
+    }
+    for (; i < hi; i += kArThreads) *reinterpret_cast<uint4*>(buf + i * 4) = ld_peer16(src + i * 16);
+  }
+  cross_barrier<W>(v, epoch + 2, timeout_ns);
+}
+
 // ---- host side ----------------------------------------------------------------------
 
 using KernelFn = const void*;
@@ -317,6 +420,17 @@ static KernelFn pick_kernel(int world, bool bf16w, int algo) {
   B2_AR_CASE(4)
   B2_AR_CASE(8)
 #undef B2_AR_CASE
+  return nullptr;
+}
+
+template <int NV>
+static KernelFn pick_inplace_kernel(int world) {
+  switch (world) {
+    case 1: return (KernelFn)allreduce_inplace_kernel<1, NV>;
+    case 2: return (KernelFn)allreduce_inplace_kernel<2, NV>;
+    case 4: return (KernelFn)allreduce_inplace_kernel<4, NV>;
+    case 8: return (KernelFn)allreduce_inplace_kernel<8, NV>;
+  }
   return nullptr;
 }
 
@@ -347,7 +461,21 @@ static int pick_blocks(long long npack, int max_blocks) {
 
 }  // namespace b2
 
+struct b2_opened_handle {  // one cudaIpcOpenMemHandle per distinct peer allocation
+  int peer;
+  unsigned char handle[B2_IPC_HANDLE_BYTES];
+  char* base;
+};
+
+struct b2_registration {
+  bool live = false;
+  size_t bytes = 0;
+  char* ptr[B2_MAX_WORLD] = {nullptr};  // the registered buffer of every rank, as mapped here
+};
+
 struct b2_comm {
+  std::vector<b2_opened_handle> peer_allocs;
+  std::vector<b2_registration> regs;
   int rank = 0, world = 1, device = 0;
   size_t half_bytes = 0;
   char* base[B2_MAX_WORLD] = {nullptr};  // mapped symmetric allocation of every rank
@@ -458,6 +586,128 @@ extern "C" int b2_allreduce(b2_comm* c, void* buf, int64_t numel, int wire_dtype
   return B2_OK;
 }
 
+
+// Base address and size of the cudaMalloc allocation that contains ptr (driver entry point
+// resolved through the runtime, so the library has no link-time dependency on libcuda).
+static int allocation_range(const void* ptr, char** base, size_t* size) {
+  using namespace b2;
+  typedef int (*GetRange)(unsigned long long*, size_t*, unsigned long long);
+  static GetRange fn = nullptr;
+  if (!fn) {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    B2_CUDA_CHECK(cudaGetDriverEntryPoint("cuMemGetAddressRange", &f, cudaEnableDefault, &q));
+    if (!f || q != cudaDriverEntryPointSuccess)
+      return fail(B2_ERR_CUDA, "comm_export: cuMemGetAddressRange is not available from this driver");
+    fn = (GetRange)f;
+  }
+  unsigned long long b = 0;
+  size_t sz = 0;
+  const int rc = fn(&b, &sz, (unsigned long long)(uintptr_t)ptr);
+  if (rc != 0) return fail(B2_ERR_CUDA, "comm_export: cuMemGetAddressRange failed with CUresult %d", rc);
+  *base = (char*)(uintptr_t)b;
+  *size = sz;
+  return B2_OK;
+}
+
+extern "C" int b2_comm_export(b2_comm* c, const void* ptr, void* handle_out, uint64_t* offset_out) {
+  using namespace b2;
+  B2_REQUIRE(c && ptr && handle_out && offset_out, "comm_export: null pointer");
+  char* base = nullptr;
+  size_t size = 0;
+  int rc = allocation_range(ptr, &base, &size);
+  if (rc != B2_OK) return rc;
+  cudaIpcMemHandle_t h;
+  B2_CUDA_CHECK(cudaIpcGetMemHandle(&h, base));
+  std::memcpy(handle_out, &h, sizeof(h));
+  *offset_out = (uint64_t)((const char*)ptr - base);
+  return B2_OK;
+}
+
+extern "C" int b2_comm_register(b2_comm* c, void* local_ptr, size_t bytes, const void* handles,
+                                const uint64_t* offsets, int* reg_id_out) {
+  using namespace b2;
+  B2_REQUIRE(c && local_ptr && reg_id_out, "comm_register: null pointer");
+  B2_REQUIRE(c->world == 1 || (handles && offsets), "comm_register: null handles/offsets");
+  B2_REQUIRE((((uintptr_t)local_ptr) & 15) == 0, "comm_register: buffer must be 16-byte aligned");
+  if (!c->opened && c->world > 1) return fail(B2_ERR_STATE, "comm_register: peers are not opened yet");
+  b2_registration reg;
+  reg.live = true;
+  reg.bytes = bytes;
+  for (int r = 0; r < c->world; ++r) {
+    if (r == c->rank) {
+      reg.ptr[r] = (char*)local_ptr;
+      continue;
+    }
+    const unsigned char* h = (const unsigned char*)handles + (size_t)r * B2_IPC_HANDLE_BYTES;
+    char* base = nullptr;
+    for (auto& o : c->peer_allocs)
+      if (o.peer == r && std::memcmp(o.handle, h, B2_IPC_HANDLE_BYTES) == 0) base = o.base;
+    if (!base) {
+      cudaIpcMemHandle_t ih;
+      std::memcpy(&ih, h, sizeof(ih));
+      B2_CUDA_CHECK(cudaIpcOpenMemHandle((void**)&base, ih, cudaIpcMemLazyEnablePeerAccess));
+      b2_opened_handle o;
+      o.peer = r;
+      std::memcpy(o.handle, h, B2_IPC_HANDLE_BYTES);
+      o.base = base;
+      c->peer_allocs.push_back(o);
+    }
+    reg.ptr[r] = base + offsets[r];
+    B2_REQUIRE((((uintptr_t)reg.ptr[r]) & 15) == 0, "comm_register: peer %d buffer is not 16-byte aligned", r);
+  }
+  for (size_t i = 0; i < c->regs.size(); ++i) {
+    if (!c->regs[i].live) {
+      c->regs[i] = reg;
+      *reg_id_out = (int)i;
+      return B2_OK;
+    }
+  }
+  c->regs.push_back(reg);
+  *reg_id_out = (int)c->regs.size() - 1;
+  return B2_OK;
+}
+
+extern "C" int b2_comm_unregister(b2_comm* c, int reg_id) {
+  using namespace b2;
+  B2_REQUIRE(c && reg_id >= 0 && reg_id < (int)c->regs.size() && c->regs[reg_id].live,
+             "comm_unregister: unknown registration %d", reg_id);
+  c->regs[reg_id].live = false;  // mappings stay cached: the allocation may hold other buffers
+  return B2_OK;
+}
+
+extern "C" int b2_allreduce_registered(b2_comm* c, int reg_id, int64_t numel, float scale,
+                                       b2_stream_t stream) {
+  using namespace b2;
+  B2_REQUIRE(c && reg_id >= 0 && reg_id < (int)c->regs.size() && c->regs[reg_id].live,
+             "allreduce_registered: unknown registration %d", reg_id);
+  const b2_registration& reg = c->regs[reg_id];
+  B2_REQUIRE(numel >= 0 && (size_t)numel * 4 <= reg.bytes,
+             "allreduce_registered: %lld elements exceed the registered %zu bytes", (long long)numel, reg.bytes);
+  if (numel == 0) return B2_OK;
+  ArArgs<1> args;
+  RankView& v = args.v[0];
+  v.buf = (float*)reg.ptr[c->rank];
+  v.rank = c->rank;
+  for (int r = 0; r < B2_MAX_WORLD; ++r) {
+    const int k = r < c->world ? r : c->rank;
+    v.stage[r] = reg.ptr[k];
+    v.flags[r] = (uint32_t*)c->base[k];
+  }
+  v.status = (uint32_t*)(c->base[c->rank] + kStatusOff);
+  KernelFn fn = pick_inplace_kernel<1>(c->world);
+  if (!fn) return fail(B2_ERR_INVALID, "allreduce_registered: no kernel for world %d", c->world);
+  const int nb = pick_blocks(numel / 4 / c->world, c->max_blocks);
+  long long n_arg = numel;
+  float scale_arg = scale;
+  uint32_t epoch = c->epoch;
+  unsigned long long to = c->timeout_ns;
+  void* kargs[] = {&args, &n_arg, &scale_arg, &epoch, &to};
+  B2_CUDA_CHECK(cudaLaunchKernel(fn, dim3(nb), dim3(kArThreads), kargs, 0, (cudaStream_t)stream));
+  c->epoch += 3;
+  return B2_OK;
+}
+
 extern "C" int b2_comm_status(b2_comm* c) {
   using namespace b2;
   B2_REQUIRE(c, "comm_status: null comm");
@@ -471,6 +721,7 @@ extern "C" int b2_comm_status(b2_comm* c) {
 extern "C" int b2_comm_destroy(b2_comm* c) {
   using namespace b2;
   if (!c) return B2_OK;
+  for (auto& h : c->peer_allocs) cudaIpcCloseMemHandle(h.base);
   for (int r = 0; r < c->world; ++r) {
     if (!c->base[r]) continue;
     if (r == c->rank) cudaFree(c->base[r]); else cudaIpcCloseMemHandle(c->base[r]);
@@ -491,7 +742,10 @@ extern "C" int b2_allreduce_emulated(void* const* bufs_host, int world, int64_t 
   using namespace b2;
   B2_REQUIRE(bufs_host && staging, "allreduce_emulated: null pointer");
   B2_REQUIRE(world == 1 || world == 2 || world == 4 || world == 8, "allreduce_emulated: world %d", world);
-  B2_REQUIRE(algo == B2_ALGO_ONE_SHOT || algo == B2_ALGO_TWO_SHOT, "allreduce_emulated: algo %d", algo);
+  B2_REQUIRE(algo == B2_ALGO_ONE_SHOT || algo == B2_ALGO_TWO_SHOT || algo == B2_ALGO_TWO_SHOT_INPLACE,
+             "allreduce_emulated: algo %d", algo);
+  B2_REQUIRE(algo != B2_ALGO_TWO_SHOT_INPLACE || wire_dtype == B2_F32,
+             "allreduce_emulated: the in-place algorithm is fp32 on the wire");
   B2_REQUIRE(wire_dtype == B2_F32 || wire_dtype == B2_BF16, "allreduce_emulated: wire dtype");
   B2_REQUIRE(numel > 0, "allreduce_emulated: numel must be positive");
   const bool bf16w = wire_dtype == B2_BF16;
@@ -511,12 +765,13 @@ extern "C" int b2_allreduce_emulated(void* const* bufs_host, int world, int64_t 
     v.rank = me;
     for (int k = 0; k < B2_MAX_WORLD; ++k) {
       char* base = (char*)staging + (size_t)(k < world ? k : me) * per_rank;
-      v.stage[k] = base + kPadBytes;
+      v.stage[k] = (algo == B2_ALGO_TWO_SHOT_INPLACE) ? (char*)bufs_host[k < world ? k : me] : base + kPadBytes;
       v.flags[k] = (uint32_t*)base;
     }
     v.status = (uint32_t*)((char*)staging + (size_t)me * per_rank + kStatusOff);
   }
-  KernelFn fn = pick_kernel<B2_MAX_WORLD>(world, bf16w, algo);
+  KernelFn fn = (algo == B2_ALGO_TWO_SHOT_INPLACE) ? pick_inplace_kernel<B2_MAX_WORLD>(world)
+                                                   : pick_kernel<B2_MAX_WORLD>(world, bf16w, algo);
   // The virtual ranks' CTAs wait on one another, so they must all be resident: cooperative
   // launch, and few enough CTAs (<= 1 per SM with 512 threads is always resident on 148 SMs).
   int nb = pick_blocks(numel / epp, 16);

@@ -168,7 +168,8 @@ typedef struct b2_comm b2_comm;
 #define B2_IPC_HANDLE_BYTES 64
 #define B2_MAX_WORLD 8
 
-enum b2_algo { B2_ALGO_AUTO = 0, B2_ALGO_ONE_SHOT = 1, B2_ALGO_TWO_SHOT = 2 };
+enum b2_algo { B2_ALGO_AUTO = 0, B2_ALGO_ONE_SHOT = 1, B2_ALGO_TWO_SHOT = 2,
+               B2_ALGO_TWO_SHOT_INPLACE = 3 /* b2_allreduce_registered / emulation only */ };
 
 /* Allocates this rank's symmetric staging buffer (2 halves of staging_bytes, used
  * alternately) and its flag pad on the CURRENT device. world in {1,2,4,8}. */
@@ -187,6 +188,20 @@ int64_t b2_comm_max_numel(b2_comm* c, int wire_dtype);
  * All ranks must call with the same numel/wire/algo in the same order. */
 int b2_allreduce(b2_comm* c, void* buf, int64_t numel, int wire_dtype, float scale,
                  int algo, b2_stream_t stream);
+/* Zero-copy path for buffers that live across steps (DDP buckets after the Reducer's rebuild;
+ * SURVEY.md 8f row 2). Each rank exports the cudaMalloc allocation that contains its buffer
+ * (b2_comm_export: 64-byte handle + byte offset of ptr inside that allocation), the host
+ * all-gathers both, and b2_comm_register maps the peers' buffers. b2_allreduce_registered then
+ * runs two-shot IN PLACE on the registered buffers: no staging copy, three cross-GPU barriers,
+ * fp32 on the wire, same rank-ordered sum (bit-identical to b2_allreduce). The buffer must stay
+ * allocated until b2_comm_unregister; memory from CUDA's virtual-memory allocators
+ * (expandable segments) cannot be exported and has to use b2_allreduce. */
+int b2_comm_export(b2_comm* c, const void* ptr, void* handle_out, uint64_t* offset_out);
+int b2_comm_register(b2_comm* c, void* local_ptr, size_t bytes, const void* handles,
+                     const uint64_t* offsets, int* reg_id_out);
+int b2_comm_unregister(b2_comm* c, int reg_id);
+int b2_allreduce_registered(b2_comm* c, int reg_id, int64_t numel, float scale,
+                            b2_stream_t stream);
 /* 0, or B2_ERR_TIMEOUT once a kernel gave up waiting for a peer (sticky). */
 int b2_comm_status(b2_comm* c);
 int b2_comm_destroy(b2_comm* c);

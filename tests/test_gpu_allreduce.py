@@ -41,7 +41,7 @@ def emulated(bufs_np, wire, algo, scale=None):
     return [b.cpu().numpy() for b in bufs]
 
 
-@pytest.mark.parametrize("algo", [1, 2])
+@pytest.mark.parametrize("algo", [1, 2, 3])
 @pytest.mark.parametrize("name", list(ALLREDUCE_CASES))
 def test_emulated_matches_golden_bit_exact(golden, name, algo):
     w, n, seed = ALLREDUCE_CASES[name]
@@ -62,12 +62,23 @@ def test_emulated_sizes_wires_algos(w, algo, wire, n):
         np.testing.assert_array_equal(out[r], ref, err_msg=f"rank {r}")
 
 
+@pytest.mark.parametrize("w", [1, 2, 4, 8])
+@pytest.mark.parametrize("n", [1, 3, 4, 1023, 8 * 512 * 4 * 3 + 5, 1 << 20])
+def test_emulated_in_place_two_shot(w, n):
+    """The zero-copy algorithm (buckets mapped by peers, reduced in place, three barriers)."""
+    bufs = allreduce_inputs(w, n, 300 + n % 97)
+    out = emulated(bufs, 0, 3)
+    ref = O.allreduce_mean(bufs)
+    for r in range(w):
+        np.testing.assert_array_equal(out[r], ref, err_msg=f"rank {r}")
+
+
 def test_emulated_large_bucket_25mib():
     """A DDP-sized bucket (25 MiB fp32) at W=8, both algorithms give the same bits."""
     w, n = 8, (25 << 20) // 4
     bufs = allreduce_inputs(w, n, 7)
     ref = O.allreduce_mean(bufs)
-    for algo in (1, 2):
+    for algo in (1, 2, 3):
         out = emulated(bufs, 0, algo)
         for r in range(w):
             np.testing.assert_array_equal(out[r], ref)
@@ -117,6 +128,17 @@ def _worker(rank, world, port, q):
                     torch.cuda.synchronize()
                     ref = O.allreduce_mean(bufs) if wname == "fp32" else O.allreduce_mean_bf16_wire(bufs)
                     results[(n, wname, algo)] = bool(np.array_equal(x.cpu().numpy(), ref))
+        # zero-copy path: a persistent buffer registered for peer access, reduced in place, reused
+        for n in (5, 4099, (6 << 20) // 4 + 3):
+            x = torch.empty(n, device="cuda")
+            reg = comm.register(x)
+            for rep in range(3):
+                bufs = allreduce_inputs(world, n, 900 + rep + n % 89)
+                x.copy_(torch.from_numpy(bufs[rank]))
+                comm.allreduce_registered_(reg, x, 1.0 / world)
+                torch.cuda.synchronize()
+                results[(n, "registered", rep)] = bool(np.array_equal(x.cpu().numpy(), O.allreduce_mean(bufs)))
+            comm.unregister(reg)
         comm.check()
 
         # DDP comm hook vs stock DDP on the same model / data: 3 steps, identical parameters
@@ -125,14 +147,17 @@ def _worker(rank, world, port, q):
             model = torch.nn.Sequential(torch.nn.Linear(512, 2048), torch.nn.ReLU(), torch.nn.Linear(2048, 4096),
                                         torch.nn.ReLU(), torch.nn.Linear(4096, 512)).cuda()
             ddp = torch.nn.parallel.DistributedDataParallel(model, device_ids=[rank], bucket_cap_mb=4)
+            hook_state = None
             if use_hook:
-                register_p2p_comm_hook(ddp, comm=comm)
+                hook_state = register_p2p_comm_hook(ddp, comm=comm, zero_copy_min_bytes=1 << 20)
             opt = torch.optim.SGD(ddp.parameters(), lr=0.1)
             g = torch.Generator(device="cuda").manual_seed(1234 + rank)
-            for _ in range(3):
+            for _ in range(5):  # long enough for the buckets to be registered (zero-copy) on step 3
                 x = torch.randn(16, 512, device="cuda", generator=g)
                 ddp(x).square().mean().backward()
                 opt.step(); opt.zero_grad()
+            if use_hook:
+                assert hook_state._registered, "no bucket was registered for zero-copy"
             return [p.detach().clone() for p in model.parameters()]
 
         a, b = run(True), run(False)
