@@ -53,10 +53,13 @@ struct ArArgs {
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
   uint32_t v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
+}
+__device__ __forceinline__ void fence_acquire_sys() {
+  asm volatile("fence.acq_rel.sys;" ::: "memory");
 }
 // Peer (or own) staging written by another GPU during this kernel: relaxed system-scope load,
 // never the non-coherent path.
@@ -87,12 +90,14 @@ __device__ __forceinline__ void cross_barrier(const RankView& v, uint32_t epoch,
     const uint32_t* mine = v.flags[v.rank] + blockIdx.x * B2_MAX_WORLD + peer;
     const unsigned long long t0 = globaltimer_ns();
     unsigned spins = 0;
-    while ((int)(ld_acquire_sys(mine) - epoch) < 0) {
+    // poll with relaxed loads (cheap), then one acquire fence once the flag has arrived
+    while ((int)(ld_relaxed_sys(mine) - epoch) < 0) {
       if ((++spins & 1023u) == 0 && globaltimer_ns() - t0 > timeout_ns) {
         atomicExch(v.status, 1u);  // sticky; b2_comm_status reports B2_ERR_TIMEOUT
         break;
       }
     }
+    fence_acquire_sys();
   }
   __syncthreads();
 }
@@ -209,8 +214,19 @@ allreduce_kernel(const __grid_constant__ ArArgs<NV> args, long long numel, float
   if (ALGO == B2_ALGO_ONE_SHOT || W == 1) {
     const long long c = (npack + nb - 1) / nb;
     const long long lo = min((long long)b * c, npack), hi = min(lo + c, npack);
-    for (long long i = lo + tid; i < hi; i += kArThreads)
-      *reinterpret_cast<uint4*>(own + i * 16) = Wr::load_scaled(buf, i, scale);
+    {
+      constexpr int UC = 4;  // copy-in: 4 independent 16-byte (fp32) / 32-byte (bf16 wire) reads in flight
+      long long i = lo + tid;
+      for (; i + (UC - 1) * kArThreads < hi; i += UC * kArThreads) {
+        uint4 t[UC];
+#pragma unroll
+        for (int u = 0; u < UC; ++u) t[u] = Wr::load_scaled(buf, i + u * kArThreads, scale);
+#pragma unroll
+        for (int u = 0; u < UC; ++u) *reinterpret_cast<uint4*>(own + (i + u * kArThreads) * 16) = t[u];
+      }
+      for (; i < hi; i += kArThreads)
+        *reinterpret_cast<uint4*>(own + i * 16) = Wr::load_scaled(buf, i, scale);
+    }
     if (b == 0 && tid < numel - tail0) Wr::tail_store(own_tail, tid, Wr::stage1(buf, tail0 + tid, scale));
     cross_barrier<W>(v, epoch, timeout_ns);
     constexpr int U = (W >= 8) ? 2 : 4;
@@ -236,7 +252,16 @@ allreduce_kernel(const __grid_constant__ ArArgs<NV> args, long long numel, float
     for (int s = 0; s < W; ++s) {
       const long long slo = min((long long)s * Q, npack), shi = min(slo + Q, npack);
       const long long lo = min(slo + (long long)b * q, shi), hi = min(lo + q, shi);
-      for (long long i = lo + tid; i < hi; i += kArThreads)
+      constexpr int UC = 4;
+      long long i = lo + tid;
+      for (; i + (UC - 1) * kArThreads < hi; i += UC * kArThreads) {
+        uint4 t[UC];
+#pragma unroll
+        for (int u = 0; u < UC; ++u) t[u] = Wr::load_scaled(buf, i + u * kArThreads, scale);
+#pragma unroll
+        for (int u = 0; u < UC; ++u) *reinterpret_cast<uint4*>(own + (i + u * kArThreads) * 16) = t[u];
+      }
+      for (; i < hi; i += kArThreads)
         *reinterpret_cast<uint4*>(own + i * 16) = Wr::load_scaled(buf, i, scale);
     }
     if (b == 0 && tid < numel - tail0) Wr::tail_store(own_tail, tid, Wr::stage1(buf, tail0 + tid, scale));

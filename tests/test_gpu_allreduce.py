@@ -161,7 +161,9 @@ def _worker(rank, world, port, q):
             return [p.detach().clone() for p in model.parameters()]
 
         a, b = run(True), run(False)
-        worst = max(float(((x - y).abs() / (y.abs() + 1e-6)).max()) for x, y in zip(a, b))
+        # NCCL's ring/tree order differs from rank order, so after 5 SGD steps the two runs agree
+        # to fp32 rounding, not bit for bit: |x - y| <= 1e-5 |y| + 1e-7 (worst excess reported)
+        worst = max(float(((x - y).abs() - 1e-5 * y.abs()).max()) for x, y in zip(a, b))
         # replicas must stay bit-identical across ranks
         same = True
         for p in a:
@@ -196,5 +198,5 @@ def test_real_peer_memory_allreduce_and_ddp_hook():
         assert err is None, f"rank {rank}:\n{err}"
         bad = [k for k, ok in results.items() if not ok]
         assert not bad, f"rank {rank}: not bit-exact vs the rank-ordered oracle: {bad}"
-        assert worst < 1e-6, f"rank {rank}: hook vs stock DDP parameters differ by {worst}"
+        assert worst < 1e-7, f"rank {rank}: hook vs stock DDP parameters differ by {worst} beyond rtol 1e-5"
         assert same, f"rank {rank}: replicas diverged"
