@@ -84,6 +84,8 @@ class ClockSampler:
         self.proc = None
 
     def __enter__(self):
+        if os.environ.get("B2_BENCH_NO_CLOCKS") == "1":  # e.g. under ncu: no child processes
+            return self
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
@@ -218,7 +220,11 @@ def main():
         h.optimizer.kernel_events = []
     launches0 = _lib.launches
     with ClockSampler(local_rank) as clocks:
+        # cudaProfilerStart/Stop bracket the timed region so that `ncu --profile-from-start off`
+        # lists exactly these K steps' launches (no-ops when no profiler is attached)
+        torch.cuda.profiler.start()
         ms_res, _ = timed_region(h, resident, read_loss=False)
+        torch.cuda.profiler.stop()
         launches = _lib.launches - launches0
         opt_events = h.optimizer.kernel_events if args.impl == "b200" else None
         if args.impl == "b200":

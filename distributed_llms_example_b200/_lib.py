@@ -49,6 +49,8 @@ SIGNATURES = {
     "b2_adamw_plan": (_i64, [C.POINTER(AdamWTensor), C.c_int32]),
     "b2_adamw_step": (C.c_int, [_vp, C.c_int32, _i64, C.POINTER(AdamWHyper), C.c_int32, _vp, _vp]),
     "b2_adamw_step_flat": (C.c_int, [_vp, _vp, _vp, _vp, _i64, C.POINTER(AdamWHyper), _vp, _vp]),
+    "b2_grad_norm_workspace_bytes": (_sz, []),
+    "b2_grad_norm_clip": (C.c_int, [_vp, C.c_int32, _i64, _f32, _vp, _sz, _vp, _vp, _vp]),
     "b2_comm_create": (C.c_int, [_i32, _i32, _sz, C.POINTER(_vp)]),
     "b2_comm_get_handle": (C.c_int, [_vp, _vp]),
     "b2_comm_open_peers": (C.c_int, [_vp, _vp]),

@@ -173,6 +173,7 @@ class HookState:
                  zero_copy_min_bytes: Optional[int] = None, **comm_kwargs):
         self.comm = comm or default_comm(**comm_kwargs)
         self.stream = torch.cuda.Stream(device=self.comm.device)
+        self.scale = 1.0 / self.comm.world
         self.buckets_reduced = 0
         # Zero-copy: once a bucket has shown up twice at the same address on EVERY rank (the
         # Reducer's buckets are stable after its one rebuild), it is registered for peer access
@@ -227,17 +228,24 @@ def p2p_allreduce_hook(state: HookState, bucket: dist.GradBucket) -> torch.futur
     """
     comm = state.comm
     buf = bucket.buffer()
+    side = state.stream
     producer = torch.cuda.current_stream(comm.device)
-    state.stream.wait_stream(producer)
+    side.wait_stream(producer)
     reg = state.registration_for(bucket.index(), buf) if state.zero_copy else None
-    with torch.cuda.stream(state.stream):
-        if reg is not None:
-            comm.allreduce_registered_(reg, buf, 1.0 / comm.world, stream=state.stream)
-        else:
-            comm.allreduce_(buf, 1.0 / comm.world, stream=state.stream)
-        buf.record_stream(state.stream)
-        fut: torch.futures.Future[torch.Tensor] = torch.futures.Future(devices=[comm.device])
+    # This runs ~100 times per step on the autograd thread, so it avoids the (slow) stream
+    # context manager: the side stream is made current only around set_result, which records
+    # the completion event on whatever stream is current. The bucket is owned by the Reducer for
+    # the life of the DDP module, so no record_stream bookkeeping is needed.
+    if reg is not None:
+        comm.allreduce_registered_(reg, buf, state.scale, stream=side)
+    else:
+        comm.allreduce_(buf, state.scale, stream=side)
+    fut: torch.futures.Future[torch.Tensor] = torch.futures.Future(devices=[comm.device])
+    torch.cuda.set_stream(side)
+    try:
         fut.set_result(buf)
+    finally:
+        torch.cuda.set_stream(producer)
     state.buckets_reduced += 1
     return fut
 

@@ -35,7 +35,8 @@ constexpr int kArThreads = 512;
 constexpr int kArMaxBlocks = 128;                                        // rows of the flag pad
 constexpr size_t kPadBytes = 16384;                                      // flags + status word
 constexpr size_t kStatusOff = kArMaxBlocks * B2_MAX_WORLD * 4;           // after the flags
-static_assert(kStatusOff + 64 <= kPadBytes, "flag pad too small");
+constexpr size_t kGateOff = kStatusOff + 256;                            // B2_MAX_WORLD gate flags
+static_assert(kGateOff + B2_MAX_WORLD * 4 <= kPadBytes, "flag pad too small");
 
 struct RankView {
   float* buf;                        // this rank's bucket, reduced in place
@@ -100,6 +101,33 @@ __device__ __forceinline__ void cross_barrier(const RankView& v, uint32_t epoch,
     fence_acquire_sys();
   }
   __syncthreads();
+}
+
+// One tiny CTA per rank that meets its peers BEFORE the wide kernel is launched behind it on the
+// same stream: ranks reach a bucket at different times (the training step is host-bound more
+// often than not), and waiting for a late peer should cost one SM, not the 64 the data
+// kernel occupies. After the gate every rank's bucket is complete and the data kernels start
+// within launch skew of each other.
+template <int W>
+__global__ void __launch_bounds__(32, 1)
+gate_kernel(const __grid_constant__ ArArgs<1> args, uint32_t epoch, unsigned long long timeout_ns) {
+  const RankView& v = args.v[0];
+  if (threadIdx.x < W) {
+    const int peer = threadIdx.x;
+    uint32_t* gate_peer = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(v.flags[peer]) + kGateOff);
+    const uint32_t* gate_mine = reinterpret_cast<const uint32_t*>(reinterpret_cast<const char*>(v.flags[v.rank]) + kGateOff);
+    st_release_sys(gate_peer + v.rank, epoch);
+    const unsigned long long t0 = globaltimer_ns();
+    unsigned spins = 0;
+    while ((int)(ld_relaxed_sys(gate_mine + peer) - epoch) < 0) {
+      __nanosleep(100);
+      if ((++spins & 1023u) == 0 && globaltimer_ns() - t0 > timeout_ns) {
+        atomicExch(v.status, 1u);
+        break;
+      }
+    }
+    fence_acquire_sys();
+  }
 }
 
 template <bool BF16W>
@@ -341,7 +369,7 @@ allreduce_kernel(const __grid_constant__ ArArgs<NV> args, long long numel, float
 template <int W, int NV>
 __global__ void __launch_bounds__(kArThreads, 1)
 allreduce_inplace_kernel(const __grid_constant__ ArArgs<NV> args, long long numel, float scale,
-                         uint32_t epoch, unsigned long long timeout_ns) {
+                         uint32_t epoch, unsigned long long timeout_ns, int gated) {
   const RankView& v = args.v[NV == 1 ? 0 : blockIdx.y];
   const int rank = v.rank;
   const int nb = gridDim.x, b = blockIdx.x, tid = threadIdx.x;
@@ -352,7 +380,7 @@ allreduce_inplace_kernel(const __grid_constant__ ArArgs<NV> args, long long nume
   const long long q = (Q + nb - 1) / nb;
   constexpr int U = (W >= 8) ? 2 : 4;
 
-  cross_barrier<W>(v, epoch, timeout_ns);
+  if (!gated) cross_barrier<W>(v, epoch, timeout_ns);  // barrier A, unless a gate_kernel ran first
   {
     const long long slo = min((long long)rank * Q, npack), shi = min(slo + Q, npack);
     const long long lo = min(slo + (long long)b * q, shi), hi = min(lo + q, shi);
@@ -727,7 +755,14 @@ extern "C" int b2_allreduce_registered(b2_comm* c, int reg_id, int64_t numel, fl
   float scale_arg = scale;
   uint32_t epoch = c->epoch;
   unsigned long long to = c->timeout_ns;
-  void* kargs[] = {&args, &n_arg, &scale_arg, &epoch, &to};
+  int gated = c->world > 1 ? 1 : 0;
+  if (gated) {
+    KernelFn gate = c->world == 2 ? (KernelFn)gate_kernel<2>
+                  : c->world == 4 ? (KernelFn)gate_kernel<4> : (KernelFn)gate_kernel<8>;
+    void* gargs[] = {&args, &epoch, &to};
+    B2_CUDA_CHECK(cudaLaunchKernel(gate, dim3(1), dim3(32), gargs, 0, (cudaStream_t)stream));
+  }
+  void* kargs[] = {&args, &n_arg, &scale_arg, &epoch, &to, &gated};
   B2_CUDA_CHECK(cudaLaunchKernel(fn, dim3(nb), dim3(kArThreads), kargs, 0, (cudaStream_t)stream));
   c->epoch += 3;
   return B2_OK;
@@ -804,7 +839,8 @@ extern "C" int b2_allreduce_emulated(void* const* bufs_host, int world, int64_t 
   float scale_arg = scale;
   uint32_t epoch = 1;
   unsigned long long to = 5ull * 1000000000ull;
-  void* kargs[] = {&args, &n_arg, &scale_arg, &epoch, &to};
+  int gated = 0;
+  void* kargs[] = {&args, &n_arg, &scale_arg, &epoch, &to, &gated};  // staging kernels ignore the extra slot
   B2_CUDA_CHECK(cudaLaunchCooperativeKernel(fn, dim3(nb, world), dim3(kArThreads), kargs, 0, st));
   return B2_OK;
 }

@@ -179,7 +179,10 @@ class StepHarness:
                     dist.all_reduce(p.grad.data, op=dist.ReduceOp.SUM)
                     p.grad.data /= size
         if cfg.semantics == "trainer" and cfg.max_grad_norm:
-            torch.nn.utils.clip_grad_norm_(self.model.parameters(), cfg.max_grad_norm)
+            if cfg.impl == "b200":
+                self.optimizer.clip_grad_norm_(cfg.max_grad_norm)  # folded into the AdamW launch
+            else:
+                torch.nn.utils.clip_grad_norm_(self.model.parameters(), cfg.max_grad_norm)
         self.optimizer.step()
         self.scheduler.step()
         self.optimizer.zero_grad()

@@ -15,6 +15,7 @@ scripts' schedule), state_dict layout matches torch's (``step`` fp32 CPU scalar 
 from __future__ import annotations
 
 import ctypes as C
+import weakref
 from typing import Any, Callable, Iterable, Optional
 
 import numpy as np
@@ -23,7 +24,22 @@ from torch.optim.optimizer import Optimizer
 
 from . import _lib
 
-__all__ = ["AdamW"]
+__all__ = ["AdamW", "owner_of"]
+
+_LIVE: "weakref.WeakSet[AdamW]" = weakref.WeakSet()
+
+
+def owner_of(params: list) -> Optional["AdamW"]:
+    """The live b200 AdamW whose parameters-with-gradients are exactly ``params``-with-gradients
+    (used by patch.patch_clip_grad_norm to route torch.nn.utils.clip_grad_norm_)."""
+    want = {id(p) for p in params if p.grad is not None}
+    if not want:
+        return None
+    for opt in list(_LIVE):
+        have = {id(p) for g in opt.param_groups for p in g["params"] if p.grad is not None}
+        if have == want:
+            return opt
+    return None
 
 _TABLE_DTYPE = np.dtype(
     [("p", "<u8"), ("g", "<u8"), ("m", "<u8"), ("v", "<u8"), ("numel", "<i8"),
@@ -60,6 +76,7 @@ class AdamW(Optimizer):
         super().__init__(params, defaults)
         self._lib = _lib.load()
         self._plan: Optional["_Plan"] = None
+        self._all_params: Optional[list] = None
         self._table_dev: Optional[torch.Tensor] = None
         self._table_pinned: Optional[torch.Tensor] = None
         self._table_event: Optional[torch.cuda.Event] = None
@@ -69,12 +86,16 @@ class AdamW(Optimizer):
         #: when set to a list, step() appends a (start, end) CUDA event pair recorded on the
         #: launching stream tightly around the kernel launch (bench.py's roofline timing).
         self.kernel_events: Optional[list] = None
+        self._norm_ws: Optional[torch.Tensor] = None
+        _LIVE.add(self)
 
     def __setstate__(self, state: dict[str, Any]) -> None:
         super().__setstate__(state)
         self.__dict__.setdefault("_plan", None)
+        self.__dict__.setdefault("_all_params", None)
         self.__dict__.setdefault("grad_scale", None)
         self.__dict__.setdefault("kernel_events", None)
+        self.__dict__.setdefault("_norm_ws", None)
         for group in self.param_groups:
             group.setdefault("amsgrad", False)
             group.setdefault("maximize", False)
@@ -84,10 +105,12 @@ class AdamW(Optimizer):
     def add_param_group(self, param_group: dict[str, Any]) -> None:
         super().add_param_group(param_group)
         self._plan = None
+        self._all_params = None
 
     def load_state_dict(self, state_dict: dict[str, Any]) -> None:
         super().load_state_dict(state_dict)
         self._plan = None
+        self._all_params = None
 
     @staticmethod
     def _check_grad(p: torch.Tensor, g: torch.Tensor) -> None:
@@ -133,8 +156,14 @@ class AdamW(Optimizer):
         plan.pattern, plan.params, plan.device = pattern, live, device
         n = len(live)
         plan.group_of = np.asarray(group_of, dtype=np.int64)
-        plan.step_tensors = [self.state[p]["step"] for p in live]
-        plan.steps = np.asarray([int(float(t)) for t in plan.step_tensors], dtype=np.int64)
+        # torch keeps one 0-d CPU tensor per parameter for state["step"]; bumping 557 of them costs
+        # ~0.9 ms per step even with _foreach_add_. Re-home them as views of ONE flat tensor so the
+        # bump is a single vector add; state_dict() still sees a 0-d fp32 tensor per parameter.
+        old = [float(self.state[p]["step"]) for p in live]
+        plan.step_flat = torch.tensor(old, dtype=torch.float32)
+        for i, p in enumerate(live):
+            self.state[p]["step"] = plan.step_flat[i]
+        plan.steps = np.asarray([int(v) for v in old], dtype=np.int64)
         host = np.zeros(n, dtype=_TABLE_DTYPE)
         host["p"] = [p.data_ptr() for p in live]
         host["m"] = [self.state[p]["exp_avg"].data_ptr() for p in live]
@@ -171,14 +200,11 @@ class AdamW(Optimizer):
         self._table_event.record()
         plan.dirty = False
 
-    # -- step ----------------------------------------------------------------------
-    @torch.no_grad()
-    def step(self, closure: Optional[Callable[[], float]] = None):
-        loss = None
-        if closure is not None:
-            with torch.enable_grad():
-                loss = closure()
-        all_params = [p for group in self.param_groups for p in group["params"]]
+    def _refresh(self, check_params: bool = True) -> Optional["_Plan"]:
+        """Current launch plan with gradient pointers re-read (cheap when nothing moved)."""
+        all_params = self._all_params
+        if all_params is None:
+            all_params = self._all_params = [p for group in self.param_groups for p in group["params"]]
         grads = [p.grad for p in all_params]
         pattern = [g is not None for g in grads]
         plan = self._plan
@@ -186,11 +212,10 @@ class AdamW(Optimizer):
             plan = self._plan = self._rebuild_plan(all_params, grads, pattern)
         n = plan.n
         if n == 0:
-            return loss
+            return None
         live = plan.params
-        live_grads = [g for g in grads if g is not None]
-        gptrs = np.fromiter((g.data_ptr() for g in live_grads), dtype=np.uint64, count=n)
-        pptrs = np.fromiter((p.data_ptr() for p in live), dtype=np.uint64, count=n)
+        live_grads = grads if n == len(grads) else [g for g in grads if g is not None]
+        gptrs = np.array(list(map(torch.Tensor.data_ptr, live_grads)), dtype=np.uint64)
         host = plan.host
         changed = np.nonzero(gptrs != host["g"])[0]
         if changed.size:
@@ -202,12 +227,53 @@ class AdamW(Optimizer):
                     gptrs[i] = g.data_ptr()
             host["g"] = gptrs
             plan.dirty = True
-        if not np.array_equal(pptrs, host["p"]):  # p.data was re-homed (e.g. module.to(...))
-            plan = self._plan = self._rebuild_plan(all_params, grads, pattern)
-            plan.host["g"] = gptrs
-            host = plan.host
+        if check_params:
+            pptrs = np.array(list(map(torch.Tensor.data_ptr, live)), dtype=np.uint64)
+            if not np.array_equal(pptrs, host["p"]):  # p.data was re-homed (e.g. module.to(...))
+                plan = self._plan = self._rebuild_plan(all_params, grads, pattern)
+                plan.host["g"] = gptrs
+        return plan
+
+    # -- gradient clipping folded into the step ------------------------------------------
+    @torch.no_grad()
+    def clip_grad_norm_(self, max_norm: float) -> torch.Tensor:
+        """``torch.nn.utils.clip_grad_norm_(params, max_norm)`` (norm_type 2) for this optimizer's
+        parameters, as HF Trainer calls it before ``optimizer.step()`` (trainer.py:1753-1757).
+        One read-only kernel computes the global norm and ``min(1, max_norm / (norm + 1e-6))`` on
+        the device; the multiply happens inside the next ``step()``'s kernel, so ``p.grad`` itself
+        is left unscaled. Returns the total norm as a 0-d device tensor (no host sync)."""
+        plan = self._refresh(check_params=False)  # this kernel only reads gradients
+        if plan is None:
+            return torch.zeros((), dtype=torch.float32)
+        device = plan.device
+        with torch.cuda.device(device):
+            if plan.dirty:
+                self._upload_table(plan)
+            if self._norm_ws is None or self._norm_ws.device != device:
+                self._norm_ws = torch.zeros(self._lib.b2_grad_norm_workspace_bytes(), dtype=torch.uint8,
+                                            device=device)
+            out = torch.empty(2, dtype=torch.float32, device=device)  # [norm, coef]
+            _lib.check(self._lib.b2_grad_norm_clip(
+                self._table_dev.data_ptr(), plan.n, plan.total_chunks, float(max_norm),
+                self._norm_ws.data_ptr(), self._norm_ws.numel(), out.data_ptr(), out.data_ptr() + 4,
+                torch.cuda.current_stream(device).cuda_stream))
+            _lib.count_launch()
+        self.grad_scale = out[1:2]
+        return out[0]
+
+    # -- step ----------------------------------------------------------------------
+    @torch.no_grad()
+    def step(self, closure: Optional[Callable[[], float]] = None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        plan = self._refresh()
+        if plan is None:
+            return loss
+        n = plan.n
         # state["step"] += 1 for every live param, in one call; python mirror for the scalars
-        torch._foreach_add_(plan.step_tensors, 1)
+        plan.step_flat.add_(1)
         plan.steps += 1
         plan.class_step += 1
         n_h = len(plan.class_group)
@@ -243,5 +309,5 @@ class AdamW(Optimizer):
 class _Plan:
     """Cached per-optimizer launch plan (see AdamW._rebuild_plan)."""
 
-    __slots__ = ("pattern", "params", "device", "group_of", "step_tensors", "steps", "host", "class_group",
-                 "class_step", "total_chunks", "n", "dirty")
+    __slots__ = ("pattern", "params", "device", "group_of", "step_flat", "steps", "host", "class_group",
+                 "class_step", "total_chunks", "n", "dirty", "grads_checked")

@@ -67,13 +67,40 @@ def patch_ddp(**comm_kwargs) -> None:
     DDP.__init__ = __init__
 
 
-def apply(cross_entropy: bool = True, adamw: bool = True, ddp: bool = True) -> None:
+def patch_clip_grad_norm() -> None:
+    """``torch.nn.utils.clip_grad_norm_`` (what HF Trainer / Accelerate call, trainer.py:1753-1757)
+    is routed to ``AdamW.clip_grad_norm_`` when the parameters are exactly those of a live b200
+    AdamW and the call is the plain L2 clip. The scaling then happens inside the optimizer
+    kernel: ``p.grad`` is NOT rewritten (nothing between clip and step reads it in the scripts)."""
+    import torch.nn.utils as U
+
+    from .optim import owner_of
+
+    if "clip" in _saved:
+        return
+    orig = U.clip_grad_norm_
+    _saved["clip"] = orig
+
+    def clip_grad_norm_(parameters, max_norm, norm_type=2.0, error_if_nonfinite=False, foreach=None):
+        params = [parameters] if isinstance(parameters, torch.Tensor) else list(parameters)
+        if float(norm_type) == 2.0 and not error_if_nonfinite:
+            opt = owner_of(params)
+            if opt is not None:
+                return opt.clip_grad_norm_(float(max_norm))
+        return orig(params, max_norm, norm_type, error_if_nonfinite, foreach)
+
+    U.clip_grad_norm_ = clip_grad_norm_
+
+
+def apply(cross_entropy: bool = True, adamw: bool = True, ddp: bool = True, fold_clip: bool = True) -> None:
     if cross_entropy:
         patch_cross_entropy()
     if adamw:
         patch_adamw()
     if ddp:
         patch_ddp()
+    if fold_clip:
+        patch_clip_grad_norm()
 
 
 def remove() -> None:
@@ -87,4 +114,8 @@ def remove() -> None:
             torch.optim.AdamW = val
         elif key == "ddp_init":
             DDP.__init__ = val
+        elif key == "clip":
+            import torch.nn.utils as U
+
+            U.clip_grad_norm_ = val
         del _saved[key]

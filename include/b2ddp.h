@@ -153,6 +153,18 @@ int b2_adamw_step_flat(void* p, const void* g, void* m, void* v, int64_t numel,
                        const b2_adamw_hyper* hyper_host, const float* grad_scale,
                        b2_stream_t stream);
 
+/* Global L2 norm of all gradients in the table + clip coefficient, one read-only launch
+ * (SURVEY.md 8f row 1). Replaces torch.nn.utils.clip_grad_norm_ as HF Trainer calls it
+ * (SP/transformers/trainer.py:1753-1757, max_grad_norm=1.0) between sync and step for
+ * train-torchrun.py:140. norm_out[0] = ||g||_2, coef_out[0] = min(1, max_norm/(norm+1e-6));
+ * pass coef_out as grad_scale to b2_adamw_step instead of rewriting the gradients.
+ * tensors_dev is the same planned table b2_adamw_step takes. workspace:
+ * b2_grad_norm_workspace_bytes() bytes, 16-byte aligned, first 16 bytes zero before first use. */
+size_t b2_grad_norm_workspace_bytes(void);
+int b2_grad_norm_clip(const b2_adamw_tensor* tensors_dev, int32_t n_tensors, int64_t total_chunks,
+                      float max_norm, void* workspace, size_t workspace_bytes, float* norm_out,
+                      float* coef_out, b2_stream_t stream);
+
 /* ------------------------------------------------------------------------- *
  * (a) gradient mean all-reduce over NVLink peer memory
  *

@@ -151,6 +151,47 @@ def test_adamw_grad_scale_unaligned_and_flat():
         assert ulp_diff(got.cpu().numpy(), want).max() <= 2
 
 
+@pytest.mark.parametrize("grad_std", [1e-4, 1e-1])  # below / above max_norm = 1.0
+def test_clip_fold_in_matches_torch_clip_then_step(grad_std):
+    """Trainer's sequence clip_grad_norm_(1.0) -> optimizer.step(), with the clip folded into the
+    AdamW launch, against torch's clip + single-tensor AdamW; also through the patched
+    torch.nn.utils.clip_grad_norm_ entry."""
+    from distributed_llms_example_b200 import patch
+    from distributed_llms_example_b200.optim import AdamW
+
+    shapes = [(300, 257), (4099,), (64, 64, 3), (1,)]
+
+    def make():
+        torch.manual_seed(0)
+        return [torch.nn.Parameter(torch.randn(s, device=DEV) * 0.02) for s in shapes]
+
+    ours, theirs = make(), make()
+    o = AdamW(ours, lr=1e-3, weight_decay=0.01)
+    t = torch.optim.AdamW(theirs, lr=1e-3, weight_decay=0.01, foreach=False, fused=False)
+    patch.patch_clip_grad_norm()
+    try:
+        for step in range(3):
+            torch.manual_seed(50 + step)
+            for a, b in zip(ours, theirs):
+                g = torch.randn_like(a) * grad_std
+                a.grad, b.grad = g.clone(), g.clone()
+            grads_before = [a.grad.clone() for a in ours]
+            if step == 0:
+                n_o = o.clip_grad_norm_(1.0)
+            else:
+                n_o = torch.nn.utils.clip_grad_norm_(ours, 1.0)  # routed to the fold-in
+            n_t = torch.nn.utils.clip_grad_norm_(theirs, 1.0)   # not ours: stock path
+            torch.testing.assert_close(n_o, n_t, rtol=2e-6, atol=0)
+            assert all(torch.equal(a.grad, g) for a, g in zip(ours, grads_before))  # grads not rewritten
+            o.step(); t.step()
+            assert o.grad_scale is None
+        for a, b in zip(ours, theirs):
+            torch.testing.assert_close(a.detach(), b.detach(), rtol=2e-6, atol=1e-9)
+            assert ulp_diff(o.state[a]["exp_avg_sq"].cpu().numpy(), t.state[b]["exp_avg_sq"].cpu().numpy()).max() <= 64
+    finally:
+        patch.remove()
+
+
 def test_adamw_rejects_what_it_does_not_implement():
     from distributed_llms_example_b200.optim import AdamW
 
