@@ -9,7 +9,7 @@ from pathlib import Path
 from .build import LIB_PATH, build
 
 B2_F32, B2_BF16 = 0, 1
-B2_ALGO_AUTO, B2_ALGO_ONE_SHOT, B2_ALGO_TWO_SHOT, B2_ALGO_TWO_SHOT_INPLACE = 0, 1, 2, 3
+B2_ALGO_AUTO, B2_ALGO_ONE_SHOT, B2_ALGO_TWO_SHOT, B2_ALGO_TWO_SHOT_INPLACE, B2_ALGO_PUSH_INPLACE = 0, 1, 2, 3, 4
 B2_IPC_HANDLE_BYTES = 64
 B2_MAX_WORLD = 8
 B2_ADAMW_MAX_HYPERS = 16

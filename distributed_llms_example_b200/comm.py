@@ -182,7 +182,7 @@ class HookState:
             zero_copy = os.environ.get("B2_AR_ZERO_COPY", "1") != "0"
         if zero_copy_min_bytes is None:
             # measured crossover against the one-barrier staging path (profiles/allreduce_*.md)
-            dflt = (24 << 20) if self.comm.world == 2 else (8 << 20)
+            dflt = (16 << 20) if self.comm.world == 2 else (8 << 20)
             zero_copy_min_bytes = int(os.environ.get("B2_AR_ZERO_COPY_MIN_BYTES", str(dflt)))
         self.zero_copy = bool(zero_copy) and self.comm.world > 1 and self.comm.wire == "fp32"
         self.zero_copy_min_bytes = zero_copy_min_bytes

@@ -454,6 +454,97 @@ allreduce_inplace_kernel(const __grid_constant__ ArArgs<NV> args, long long nume
   cross_barrier<W>(v, epoch + 2, timeout_ns);
 }
 
+// ---- zero-copy, one pass: reduce my slice from every bucket, PUSH the result into every bucket --
+//
+// With the peers' buckets mapped, the slice owner can also WRITE the reduced values straight
+// into each peer's bucket. Reads arrive on the inbound half of the NVLink port while the
+// stores leave on the outbound half, so the two halves of two-shot overlap instead of following
+// each other, and the middle barrier disappears:
+//   gate / barrier A   every rank's bucket is complete
+//   one pass           rank r: for i in slice r: x = sum_k scale*bucket_k[i] (rank order);
+//                      bucket_k[i] = x for every k            ((W-1)/W*S in, (W-1)/W*S out)
+//   barrier C          all pushed values have landed everywhere
+// Only rank r touches slice r of any bucket during the pass (it reads an element from every
+// bucket before it overwrites that element), so there is no hazard inside the pass.
+// Weak (fire-and-forget) 16-byte store: completion and visibility are established once, by the
+// __threadfence_system() + releasing flag store of the final barrier, not per store.
+__device__ __forceinline__ void st_peer16(void* p, uint4 v) {
+  asm volatile("st.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
+template <int W, int NV>
+__global__ void __launch_bounds__(kArThreads, 1)
+allreduce_push_kernel(const __grid_constant__ ArArgs<NV> args, long long numel, float scale,
+                      uint32_t epoch, unsigned long long timeout_ns, int gated) {
+  const RankView& v = args.v[NV == 1 ? 0 : blockIdx.y];
+  const int rank = v.rank;
+  const int nb = gridDim.x, b = blockIdx.x, tid = threadIdx.x;
+  const long long npack = numel / 4;
+  const long long tail0 = npack * 4;
+  const long long Q = (npack + W - 1) / W;
+  const long long q = (Q + nb - 1) / nb;
+  constexpr int U = (W >= 8) ? 2 : 4;
+
+  if (!gated) cross_barrier<W>(v, epoch, timeout_ns);
+  const long long slo = min((long long)rank * Q, npack), shi = min(slo + Q, npack);
+  const long long lo = min(slo + (long long)b * q, shi), hi = min(lo + q, shi);
+  long long i = lo + tid;
+  for (; i + (U - 1) * kArThreads < hi; i += U * kArThreads) {
+    uint4 r[U][W];
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+#pragma unroll
+      for (int k = 0; k < W; ++k) r[u][k] = ld_stream16(v.stage[k] + (i + u * kArThreads) * 16);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      float acc[4];
+#pragma unroll
+      for (int k = 0; k < W; ++k) {
+        float x[4];
+        Wire<false>::to_f(r[u][k], x);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float t = __fmul_rn(x[e], scale);
+          acc[e] = (k == 0) ? t : __fadd_rn(acc[e], t);
+        }
+      }
+      const uint4 o = Wire<false>::from_f(acc);
+#pragma unroll
+      for (int k = 0; k < W; ++k) st_peer16(v.stage[(rank + k) % W] + (i + u * kArThreads) * 16, o);
+    }
+  }
+  for (; i < hi; i += kArThreads) {
+    float acc[4];
+#pragma unroll
+    for (int k = 0; k < W; ++k) {
+      float x[4];
+      Wire<false>::to_f(ld_stream16(v.stage[k] + i * 16), x);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float t = __fmul_rn(x[e], scale);
+        acc[e] = (k == 0) ? t : __fadd_rn(acc[e], t);
+      }
+    }
+    const uint4 o = Wire<false>::from_f(acc);
+#pragma unroll
+    for (int k = 0; k < W; ++k) st_peer16(v.stage[(rank + k) % W] + i * 16, o);
+  }
+  // tail (numel % 4): rank 0 owns it
+  if (rank == 0 && b == 0 && tid < numel - tail0) {
+    float acc = 0.f;
+#pragma unroll
+    for (int k = 0; k < W; ++k) {
+      const float t = __fmul_rn(Wire<false>::tail_load(v.stage[k] + tail0 * 4, tid), scale);
+      acc = (k == 0) ? t : __fadd_rn(acc, t);
+    }
+#pragma unroll
+    for (int k = 0; k < W; ++k) reinterpret_cast<volatile float*>(v.stage[k] + tail0 * 4)[tid] = acc;
+  }
+  __threadfence_system();  // this thread's remote stores are performed before the CTA signals
+  cross_barrier<W>(v, epoch + 1, timeout_ns);
+}
+
 // ---- host side ----------------------------------------------------------------------
 
 using KernelFn = const void*;
@@ -473,6 +564,17 @@ static KernelFn pick_kernel(int world, bool bf16w, int algo) {
   B2_AR_CASE(4)
   B2_AR_CASE(8)
 #undef B2_AR_CASE
+  return nullptr;
+}
+
+template <int NV>
+static KernelFn pick_push_kernel(int world) {
+  switch (world) {
+    case 1: return (KernelFn)allreduce_push_kernel<1, NV>;
+    case 2: return (KernelFn)allreduce_push_kernel<2, NV>;
+    case 4: return (KernelFn)allreduce_push_kernel<4, NV>;
+    case 8: return (KernelFn)allreduce_push_kernel<8, NV>;
+  }
   return nullptr;
 }
 
@@ -499,7 +601,7 @@ static long long env_ll(const char* name, long long dflt) {
 // 2(W-1)/W*S and needs two. At W=2 the bytes are equal, so one-shot always wins.
 static int pick_algo(int world, long long bytes) {
   if (world <= 2) return B2_ALGO_ONE_SHOT;
-  const long long thresh = env_ll("B2_AR_ONE_SHOT_MAX_BYTES", world == 4 ? (1ll << 20) : (512ll << 10));
+  const long long thresh = env_ll("B2_AR_ONE_SHOT_MAX_BYTES", world == 4 ? (4ll << 20) : (1ll << 20));
   return bytes <= thresh ? B2_ALGO_ONE_SHOT : B2_ALGO_TWO_SHOT;
 }
 
@@ -535,7 +637,7 @@ struct b2_comm {
   bool opened = false;
   uint32_t epoch = 1;
   int parity = 0;
-  int max_blocks = 64;
+  int max_blocks = 96;
   unsigned long long timeout_ns = 30ull * 1000000000ull;
 };
 
@@ -550,7 +652,7 @@ extern "C" int b2_comm_create(int rank, int world, size_t staging_bytes, b2_comm
   c->rank = rank;
   c->world = world;
   c->half_bytes = (staging_bytes + 255) & ~(size_t)255;
-  c->max_blocks = (int)env_ll("B2_AR_BLOCKS", 64);
+  c->max_blocks = (int)env_ll("B2_AR_BLOCKS", 96);
   if (c->max_blocks < 1) c->max_blocks = 1;
   if (c->max_blocks > kArMaxBlocks) c->max_blocks = kArMaxBlocks;
   c->timeout_ns = (unsigned long long)env_ll("B2_AR_TIMEOUT_MS", 30000) * 1000000ull;
@@ -748,7 +850,8 @@ extern "C" int b2_allreduce_registered(b2_comm* c, int reg_id, int64_t numel, fl
     v.flags[r] = (uint32_t*)c->base[k];
   }
   v.status = (uint32_t*)(c->base[c->rank] + kStatusOff);
-  KernelFn fn = pick_inplace_kernel<1>(c->world);
+  static const bool pull = env_ll("B2_AR_ZERO_COPY_PULL", 0) != 0;  // A/B knob: two-shot pull variant
+  KernelFn fn = pull ? pick_inplace_kernel<1>(c->world) : pick_push_kernel<1>(c->world);
   if (!fn) return fail(B2_ERR_INVALID, "allreduce_registered: no kernel for world %d", c->world);
   const int nb = pick_blocks(numel / 4 / c->world, c->max_blocks);
   long long n_arg = numel;
@@ -764,7 +867,7 @@ extern "C" int b2_allreduce_registered(b2_comm* c, int reg_id, int64_t numel, fl
   }
   void* kargs[] = {&args, &n_arg, &scale_arg, &epoch, &to, &gated};
   B2_CUDA_CHECK(cudaLaunchKernel(fn, dim3(nb), dim3(kArThreads), kargs, 0, (cudaStream_t)stream));
-  c->epoch += 3;
+  c->epoch += 3;  // gate, (barrier B of the pull variant,) final barrier
   return B2_OK;
 }
 
@@ -802,10 +905,10 @@ extern "C" int b2_allreduce_emulated(void* const* bufs_host, int world, int64_t 
   using namespace b2;
   B2_REQUIRE(bufs_host && staging, "allreduce_emulated: null pointer");
   B2_REQUIRE(world == 1 || world == 2 || world == 4 || world == 8, "allreduce_emulated: world %d", world);
-  B2_REQUIRE(algo == B2_ALGO_ONE_SHOT || algo == B2_ALGO_TWO_SHOT || algo == B2_ALGO_TWO_SHOT_INPLACE,
-             "allreduce_emulated: algo %d", algo);
-  B2_REQUIRE(algo != B2_ALGO_TWO_SHOT_INPLACE || wire_dtype == B2_F32,
-             "allreduce_emulated: the in-place algorithm is fp32 on the wire");
+  B2_REQUIRE(algo >= B2_ALGO_ONE_SHOT && algo <= B2_ALGO_PUSH_INPLACE, "allreduce_emulated: algo %d", algo);
+  const bool inplace = (algo == B2_ALGO_TWO_SHOT_INPLACE || algo == B2_ALGO_PUSH_INPLACE);
+  B2_REQUIRE(!inplace || wire_dtype == B2_F32,
+             "allreduce_emulated: the in-place algorithms are fp32 on the wire");
   B2_REQUIRE(wire_dtype == B2_F32 || wire_dtype == B2_BF16, "allreduce_emulated: wire dtype");
   B2_REQUIRE(numel > 0, "allreduce_emulated: numel must be positive");
   const bool bf16w = wire_dtype == B2_BF16;
@@ -825,12 +928,13 @@ extern "C" int b2_allreduce_emulated(void* const* bufs_host, int world, int64_t 
     v.rank = me;
     for (int k = 0; k < B2_MAX_WORLD; ++k) {
       char* base = (char*)staging + (size_t)(k < world ? k : me) * per_rank;
-      v.stage[k] = (algo == B2_ALGO_TWO_SHOT_INPLACE) ? (char*)bufs_host[k < world ? k : me] : base + kPadBytes;
+      v.stage[k] = inplace ? (char*)bufs_host[k < world ? k : me] : base + kPadBytes;
       v.flags[k] = (uint32_t*)base;
     }
     v.status = (uint32_t*)((char*)staging + (size_t)me * per_rank + kStatusOff);
   }
   KernelFn fn = (algo == B2_ALGO_TWO_SHOT_INPLACE) ? pick_inplace_kernel<B2_MAX_WORLD>(world)
+              : (algo == B2_ALGO_PUSH_INPLACE)     ? pick_push_kernel<B2_MAX_WORLD>(world)
                                                    : pick_kernel<B2_MAX_WORLD>(world, bf16w, algo);
   // The virtual ranks' CTAs wait on one another, so they must all be resident: cooperative
   // launch, and few enough CTAs (<= 1 per SM with 512 threads is always resident on 148 SMs).

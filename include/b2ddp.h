@@ -181,7 +181,8 @@ typedef struct b2_comm b2_comm;
 #define B2_MAX_WORLD 8
 
 enum b2_algo { B2_ALGO_AUTO = 0, B2_ALGO_ONE_SHOT = 1, B2_ALGO_TWO_SHOT = 2,
-               B2_ALGO_TWO_SHOT_INPLACE = 3 /* b2_allreduce_registered / emulation only */ };
+               B2_ALGO_TWO_SHOT_INPLACE = 3, /* registered buffers: pull variant (emulation / A-B) */
+               B2_ALGO_PUSH_INPLACE = 4      /* registered buffers: one-pass reduce + push (default) */ };
 
 /* Allocates this rank's symmetric staging buffer (2 halves of staging_bytes, used
  * alternately) and its flag pad on the CURRENT device. world in {1,2,4,8}. */
@@ -204,8 +205,10 @@ int b2_allreduce(b2_comm* c, void* buf, int64_t numel, int wire_dtype, float sca
  * SURVEY.md 8f row 2). Each rank exports the cudaMalloc allocation that contains its buffer
  * (b2_comm_export: 64-byte handle + byte offset of ptr inside that allocation), the host
  * all-gathers both, and b2_comm_register maps the peers' buffers. b2_allreduce_registered then
- * runs two-shot IN PLACE on the registered buffers: no staging copy, three cross-GPU barriers,
- * fp32 on the wire, same rank-ordered sum (bit-identical to b2_allreduce). The buffer must stay
+ * works IN PLACE on the registered buffers with no staging copy: the owner of a slice reads it
+ * from every rank's buffer, adds in rank order and pushes the result into every rank's buffer
+ * in the same pass (reads inbound, writes outbound on NVLink), between a one-CTA gate kernel and
+ * a final barrier. fp32 on the wire, same rank-ordered sum (bit-identical to b2_allreduce). The buffer must stay
  * allocated until b2_comm_unregister; memory from CUDA's virtual-memory allocators
  * (expandable segments) cannot be exported and has to use b2_allreduce. */
 int b2_comm_export(b2_comm* c, const void* ptr, void* handle_out, uint64_t* offset_out);

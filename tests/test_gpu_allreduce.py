@@ -41,7 +41,7 @@ def emulated(bufs_np, wire, algo, scale=None):
     return [b.cpu().numpy() for b in bufs]
 
 
-@pytest.mark.parametrize("algo", [1, 2, 3])
+@pytest.mark.parametrize("algo", [1, 2, 3, 4])
 @pytest.mark.parametrize("name", list(ALLREDUCE_CASES))
 def test_emulated_matches_golden_bit_exact(golden, name, algo):
     w, n, seed = ALLREDUCE_CASES[name]
@@ -62,12 +62,13 @@ def test_emulated_sizes_wires_algos(w, algo, wire, n):
         np.testing.assert_array_equal(out[r], ref, err_msg=f"rank {r}")
 
 
+@pytest.mark.parametrize("algo", [3, 4])
 @pytest.mark.parametrize("w", [1, 2, 4, 8])
 @pytest.mark.parametrize("n", [1, 3, 4, 1023, 8 * 512 * 4 * 3 + 5, 1 << 20])
-def test_emulated_in_place_two_shot(w, n):
-    """The zero-copy algorithm (buckets mapped by peers, reduced in place, three barriers)."""
+def test_emulated_in_place(w, n, algo):
+    """The zero-copy algorithms on buckets mapped by peers: 3 = two-shot pull, 4 = one-pass push."""
     bufs = allreduce_inputs(w, n, 300 + n % 97)
-    out = emulated(bufs, 0, 3)
+    out = emulated(bufs, 0, algo)
     ref = O.allreduce_mean(bufs)
     for r in range(w):
         np.testing.assert_array_equal(out[r], ref, err_msg=f"rank {r}")
@@ -78,7 +79,7 @@ def test_emulated_large_bucket_25mib():
     w, n = 8, (25 << 20) // 4
     bufs = allreduce_inputs(w, n, 7)
     ref = O.allreduce_mean(bufs)
-    for algo in (1, 2, 3):
+    for algo in (1, 2, 3, 4):
         out = emulated(bufs, 0, algo)
         for r in range(w):
             np.testing.assert_array_equal(out[r], ref)
