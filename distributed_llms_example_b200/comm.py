@@ -182,7 +182,7 @@ class HookState:
             zero_copy = os.environ.get("B2_AR_ZERO_COPY", "1") != "0"
         if zero_copy_min_bytes is None:
             # measured crossover against the one-barrier staging path (profiles/allreduce_*.md)
-            dflt = (16 << 20) if self.comm.world == 2 else (8 << 20)
+            dflt = {2: 16 << 20, 4: 8 << 20}.get(self.comm.world, 2 << 20)
             zero_copy_min_bytes = int(os.environ.get("B2_AR_ZERO_COPY_MIN_BYTES", str(dflt)))
         self.zero_copy = bool(zero_copy) and self.comm.world > 1 and self.comm.wire == "fp32"
         self.zero_copy_min_bytes = zero_copy_min_bytes
@@ -274,6 +274,23 @@ def average_gradients(model: torch.nn.Module, comm: Optional[P2PComm] = None) ->
         return
     if any(g.dtype != torch.float32 for g in grads):
         raise NotImplementedError("average_gradients: fp32 gradients only")
-    flat = torch.cat([g.reshape(-1) for g in grads])
-    comm.allreduce_(flat, 1.0 / comm.world)
-    torch._foreach_copy_(grads, [c.view_as(g) for c, g in zip(flat.split([g.numel() for g in grads]), grads)])
+    sizes = [g.numel() for g in grads]
+    total = sum(sizes)
+    # One persistent flat buffer per (communicator, size), registered once for peer access, so
+    # every later step is: pack -> zero-copy all-reduce in place -> unpack.
+    cache = getattr(comm, "_flat_cache", None)
+    if cache is None:
+        cache = comm._flat_cache = {}
+    entry = cache.get(total)
+    if entry is None:
+        flat = torch.empty(total, dtype=torch.float32, device=comm.device)
+        reg = comm.register(flat) if comm.world > 1 and comm.wire == "fp32" else None
+        entry = cache[total] = (flat, reg)
+    flat, reg = entry
+    views = list(flat.split(sizes))
+    torch._foreach_copy_(views, [g.reshape(-1) for g in grads])
+    if reg is not None:
+        comm.allreduce_registered_(reg, flat, 1.0 / comm.world)
+    else:
+        comm.allreduce_(flat, 1.0 / comm.world)
+    torch._foreach_copy_(grads, [v.view_as(g) for v, g in zip(views, grads)])

@@ -140,6 +140,25 @@ def _worker(rank, world, port, q):
                 torch.cuda.synchronize()
                 results[(n, "registered", rep)] = bool(np.array_equal(x.cpu().numpy(), O.allreduce_mean(bufs)))
             comm.unregister(reg)
+        # train-task.py's average_gradients(model): one flat exchange, bit-exact vs the oracle, and
+        # the second call reuses the registered flat buffer
+        from distributed_llms_example_b200.comm import average_gradients
+
+        torch.manual_seed(0)
+        mlp = torch.nn.Sequential(torch.nn.Linear(300, 700), torch.nn.Linear(700, 33, bias=False)).cuda()
+        for rep in range(2):
+            g = torch.Generator(device="cuda").manual_seed(4000 + 10 * rep + rank)
+            for p in mlp.parameters():
+                p.grad = torch.randn(p.shape, device="cuda", generator=g) * 1e-2
+            want = []
+            for p in mlp.parameters():
+                parts = [torch.empty_like(p.grad) for _ in range(world)]
+                dist.all_gather(parts, p.grad)
+                want.append(O.allreduce_mean([t.cpu().numpy().reshape(-1) for t in parts]))
+            average_gradients(mlp, comm)
+            torch.cuda.synchronize()
+            ok = all(np.array_equal(p.grad.cpu().numpy().reshape(-1), w) for p, w in zip(mlp.parameters(), want))
+            results[("average_gradients", rep)] = bool(ok)
         comm.check()
 
         # DDP comm hook vs stock DDP on the same model / data: 3 steps, identical parameters
