@@ -143,6 +143,41 @@ def timed_region(harness, steps_batches, *, read_loss: bool):
     return float(ms.item()), (last if read_loss else float(last.item()))
 
 
+def grad_sync_probe(harness, impl: str, world: int, bucket_mb: float = 25.0, iters: int = 20) -> dict:
+    """Second half of BASELINE.json's metric: achieved gradient-sync bus GB/s against NVLink peak,
+    measured live on a DDP-sized fp32 bucket (25 MiB), device-timed, max over ranks. For impl=b200
+    the bucket is registered for peer access like the Reducer's buckets are from step 3 on."""
+    dev = harness.device
+    n = int(bucket_mb * (1 << 20)) // 4
+    x = torch.randn(n, device=dev) * 1e-2
+    if impl == "b200":
+        comm = harness.hook_state.comm if harness.hook_state is not None else harness.comm
+        reg = comm.register(x)
+        fn = lambda: comm.allreduce_registered_(reg, x, 1.0 / world)  # noqa: E731
+    else:
+        def fn():
+            x.div_(world)
+            dist.all_reduce(x)
+    for _ in range(5):
+        fn()
+    torch.cuda.synchronize(dev)
+    dist.barrier()
+    torch.cuda.synchronize(dev)
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(iters):
+        fn()
+    b.record()
+    b.synchronize()
+    t = torch.tensor([a.elapsed_time(b) / iters], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    bus = n * 4 * 2 * (world - 1) / world / ms / 1e6
+    return {"bucket_mb": bucket_mb, "us_per_bucket": ms * 1e3, "bus_gbs": bus, "nvlink_peak_gbs": 900.0,
+            "frac_of_nvlink_peak": bus / 900.0, "frac_of_measured_peer_copy_770": bus / 770.0,
+            "impl": "zero-copy one-pass push over peer-mapped buckets" if impl == "b200" else "nccl div_ + all_reduce"}
+
+
 def run_cpu(args, steps: int, warmup: int):
     """The reference's CPU path: the same harness with stock torch ops on the host cores, fp32,
     one sample per step (a bounded sample of the workload). Returns (samples/s, threads, desc)."""
@@ -196,6 +231,8 @@ def main():
                          "use --impl reference for the CPU arm")
     torch.cuda.set_device(local_rank)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"  # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     from distributed_llms_example_b200 import _lib
@@ -261,6 +298,8 @@ def main():
            "gpu_launches": launches if args.impl == "b200" else 0,
            "clocks": clocks.summary(), "roofline": roofline, "final_loss": last_loss,
            "params": n_params, "lib": str(_lib.lib_path().name) if args.impl == "b200" else None}
+    if world > 1:
+        out["grad_sync"] = grad_sync_probe(h, args.impl, world)
     h.close()
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline and args.impl == "b200":
