@@ -235,3 +235,119 @@ def test_product_refuses_cpu_tensors_instead_of_falling_back():
         cross_entropy(torch.zeros(2, 8), torch.zeros(2, dtype=torch.int64))
     with pytest.raises(RuntimeError):
         StepHarness(StepConfig(model="t5-small", impl="b200", device="cpu"))
+
+
+# ---- zero-copy registration vote (no GPU: a stand-in communicator records the calls) -----------
+class _FakeComm:
+    """Duck-types the four members HookState.registration_for touches."""
+
+    def __init__(self, rank, world, exportable=True):
+        self.rank, self.world, self.group, self.wire = rank, world, None, "fp32"
+        self.device = torch.device("cpu")
+        self.exportable = exportable
+        self.registered = []
+
+    def export(self, buf):
+        from distributed_llms_example_b200 import _lib
+
+        if not self.exportable:
+            raise _lib.B2Error(-2, "cannot export")
+        return (bytes([self.rank]) * 64, 512 * self.rank)
+
+    def register(self, buf, peers=None):
+        self.registered.append(peers)
+        return len(self.registered) - 1
+
+
+class _Buf:
+    def __init__(self, ptr, n):
+        self._p, self._n = ptr, n
+
+    def data_ptr(self):
+        return self._p
+
+    def numel(self):
+        return self._n
+
+
+def _vote_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from distributed_llms_example_b200.comm import HookState
+
+        def state(exportable=True):
+            st = HookState.__new__(HookState)  # skip the CUDA stream/event members: host logic only
+            st.comm = _FakeComm(rank, world, exportable)
+            st.zero_copy, st.zero_copy_min_bytes = True, 1 << 20
+            st._last_seen, st._registered = {}, {}
+            return st
+
+        big = 1 << 20  # elements -> 4 MiB
+        st = state()
+        # step 0: first sighting -> nobody registers; step 1: same address everywhere -> register
+        r0 = st.registration_for(3, _Buf(0x1000 + rank, big))
+        r1 = st.registration_for(3, _Buf(0x1000 + rank, big))
+        r2 = st.registration_for(3, _Buf(0x1000 + rank, big))  # cached, no collective
+        peers = st.comm.registered[0]
+        ok_basic = (r0 is None and r1 == 0 and r2 == 0 and
+                    peers == [(bytes([r]) * 64, 512 * r) for r in range(world)])
+        # a bucket below the size threshold never votes
+        ok_small = st.registration_for(0, _Buf(0x2000, 16)) is None and 0 not in st._last_seen
+        # one rank sees the bucket move between steps -> all ranks decline together, then agree later
+        st2 = state()
+        st2.registration_for(5, _Buf(0x3000, big))
+        moved = st2.registration_for(5, _Buf(0x3000 + (0x100 if rank == 1 else 0), big))
+        again = st2.registration_for(5, _Buf(0x3000 + (0x100 if rank == 1 else 0), big))
+        ok_move = moved is None and again == 0
+        # memory that cannot be exported on one rank (expandable segments) -> nobody registers
+        st3 = state(exportable=(rank != 0))
+        st3.registration_for(7, _Buf(0x4000, big))
+        ok_noexport = st3.registration_for(7, _Buf(0x4000, big)) is None and not st3.comm.registered
+        # a registered bucket that moves is an error, not a silent divergence
+        try:
+            st.registration_for(3, _Buf(0x9999, big))
+            ok_raise = False
+        except RuntimeError:
+            ok_raise = True
+        q.put((rank, ok_basic, ok_small, ok_move, ok_noexport, ok_raise, None))
+    except Exception:
+        import traceback
+
+        q.put((rank, False, False, False, False, False, traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_zero_copy_registration_is_a_collective_agreement():
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_vote_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    outs = [q.get(timeout=300) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, *oks, err in outs:
+        assert err is None, f"rank {rank}:\n{err}"
+        assert all(oks), (rank, oks)
+
+
+def test_bench_reference_arm_prints_one_json_line():
+    """`bench.py --impl reference` (the CPU arm the driver runs next to ours) on the smallest model."""
+    import json
+    import subprocess
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--model", "t5-small",
+                          "--steps", "1", "--warmup", "1"], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [l for l in out.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["metric"] == "train_samples_per_second" and d["value"] > 0
+    assert d["cpu_baseline"]["kind"] in ("port", "reference") and d["cpu_baseline"]["cores"] >= 1
+    assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["higher_is_better"] is True
