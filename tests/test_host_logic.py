@@ -351,3 +351,53 @@ def test_bench_reference_arm_prints_one_json_line():
     assert d["impl"] == "reference" and d["metric"] == "train_samples_per_second" and d["value"] > 0
     assert d["cpu_baseline"]["kind"] in ("port", "reference") and d["cpu_baseline"]["cores"] >= 1
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["higher_is_better"] is True
+
+
+# ---- BASELINE config 1: t5-small, torchrun-style world size 2 over gloo on CPU -------------------
+def _config1_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.set_num_threads(2)
+        from distributed_llms_example_b200.harness import StepConfig, StepHarness
+
+        # small sequences keep the CPU test short; the step logic is what is under test
+        import distributed_llms_example_b200.harness as H
+
+        real = H.make_features
+        H.make_features = lambda n, **kw: real(n, src_len=48, tgt_len=16, **kw)
+        h = StepHarness(StepConfig(model="t5-small", semantics="trainer", impl="stock", device="cpu", batch_size=1,
+                                   grad_accum=2, label_mode="MASK", bf16=False, dropout=0.0, total_steps=10))
+        batches = h.host_batches(3 * 2)
+        losses = [float(h.step(batches[i * 2:(i + 1) * 2])) for i in range(3)]
+        flat = torch.cat([p.detach().reshape(-1) for p in h.model.parameters()])
+        parts = [torch.empty_like(flat) for _ in range(world)]
+        dist.all_gather(parts, flat)
+        q.put((rank, losses, all(torch.equal(parts[0], p) for p in parts), h.ddp is not None, None))
+    except Exception:
+        import traceback
+
+        q.put((rank, [], False, False, traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_config1_reference_cpu_path_world_2_gloo():
+    """The reference's own CPU-runnable case (BASELINE.json configs[0]) through the step harness:
+    DDP over gloo, gradient accumulation with no_sync, clip, AdamW, schedule. Ranks see different
+    data (seed 1234 + rank), so losses differ, but the replicas must stay bit-identical."""
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_config1_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    outs = sorted(q.get(timeout=600) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+    for rank, losses, same, wrapped, err in outs:
+        assert err is None, f"rank {rank}:\n{err}"
+        assert wrapped and same and len(losses) == 3 and all(np.isfinite(losses))
+    assert outs[0][1] != outs[1][1]  # different shards of synthetic data per rank
