@@ -232,6 +232,9 @@ def bench_allreduce(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     comm = P2PComm(staging_bytes=args.staging_mb << 20)
+    nvls = world > 1 and comm.enable_nvls()
+    if rank == 0:
+        print(json.dumps({"nvls_enabled": bool(nvls), "nvls_error": comm.nvls_error}), flush=True)
 
     def timed(fn, iters, warmup):
         for _ in range(warmup):
@@ -262,6 +265,8 @@ def bench_allreduce(args):
                     continue
                 ms = timed(lambda: comm.allreduce_(x, 1.0 / world, wire=wire, algo=algo), iters, args.warmup)
                 rows.append((f"b200_{wire}_{algo}", ms))
+        if world > 1 and nvls:
+            rows.append(("b200_fp32_nvls", timed(lambda: comm.allreduce_nvls_(x, 1.0 / world), iters, args.warmup)))
         if world > 1:
             reg = comm.register(x)
             rows.append(("b200_fp32_zero_copy_inplace",

@@ -60,6 +60,12 @@ SIGNATURES = {
     "b2_comm_register": (C.c_int, [_vp, _vp, _sz, _vp, C.POINTER(C.c_uint64), C.POINTER(C.c_int)]),
     "b2_comm_unregister": (C.c_int, [_vp, _i32]),
     "b2_allreduce_registered": (C.c_int, [_vp, _i32, _i64, _f32, _vp]),
+    "b2_nvls_supported": (C.c_int, [C.POINTER(C.c_int)]),
+    "b2_nvls_create": (C.c_int, [_vp, _sz, C.POINTER(C.c_int), C.POINTER(_sz)]),
+    "b2_nvls_import": (C.c_int, [_vp, C.c_int, _sz]),
+    "b2_nvls_add_device": (C.c_int, [_vp]),
+    "b2_nvls_bind": (C.c_int, [_vp]),
+    "b2_allreduce_nvls": (C.c_int, [_vp, _vp, _i64, _f32, _vp]),
     "b2_comm_status": (C.c_int, [_vp]),
     "b2_comm_destroy": (C.c_int, [_vp]),
     "b2_allreduce_emulated_scratch_bytes": (_sz, [_i32, _i64]),

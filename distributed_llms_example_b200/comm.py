@@ -59,6 +59,7 @@ class P2PComm:
         if wire not in _WIRE or algo not in _ALGO:
             raise ValueError(f"wire must be one of {list(_WIRE)}, algo one of {list(_ALGO)}")
         self.group, self.wire, self.algo = group, wire, algo
+        self.nvls, self.nvls_error = False, ""
         self.device = torch.device("cuda", torch.cuda.current_device())
         if staging_bytes is None:
             staging_bytes = int(os.environ.get("B2_AR_STAGING_MB", "64")) << 20
@@ -128,6 +129,91 @@ class P2PComm:
         s = (stream or torch.cuda.current_stream(self.device)).cuda_stream
         _lib.check(self._lib.b2_allreduce_registered(self._ctx, reg_id, tensor.numel(), float(scale), s))
         _lib.count_launch(2 if self.world > 1 else 1)  # gate + data kernel
+        return tensor
+
+    # -- in-switch reduction (NVLS) -------------------------------------------------------------
+    def enable_nvls(self, nbytes: Optional[int] = None) -> bool:
+        """Collective. Builds the multicast object and binds one buffer per rank; returns False
+        (on every rank) if any rank's device or driver cannot do it, so callers stay in step."""
+        if self.nvls:
+            return True
+        if self.world < 2:
+            return False
+        import socket
+        import tempfile
+
+        nbytes = nbytes or (int(os.environ.get("B2_AR_NVLS_MB", "64")) << 20)
+        lib, ctx, ok = self._lib, self._ctx, True
+        sup = C.c_int(0)
+        ok = lib.b2_nvls_supported(C.byref(sup)) == 0 and sup.value == 1
+
+        def agree(flag: bool) -> bool:
+            votes: list = [None] * self.world
+            dist.all_gather_object(votes, bool(flag), group=self.group)
+            return all(votes)
+
+        if not agree(ok):
+            return False
+        # 1. rank 0 creates the multicast object; its POSIX fd travels over a Unix socket
+        info = [None]
+        srv = None
+        fd = C.c_int(-1)
+        rounded = C.c_size_t(0)
+        if self.rank == 0:
+            ok = lib.b2_nvls_create(ctx, nbytes, C.byref(fd), C.byref(rounded)) == 0
+            if ok:
+                path = os.path.join(tempfile.gettempdir(), f"b2ddp-nvls-{os.getpid()}-{id(self):x}.sock")
+                srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                srv.bind(path)
+                srv.listen(self.world)
+                info = [(path, rounded.value)]
+            else:
+                self.nvls_error = lib.b2_last_error().decode(errors="replace")
+        dist.broadcast_object_list(info, src=dist.get_global_rank(self.group, 0) if self.group else 0,
+                                   group=self.group)
+        if info[0] is None:
+            return False
+        path, rounded_bytes = info[0]
+        if self.rank == 0:
+            for _ in range(self.world - 1):
+                conn, _addr = srv.accept()
+                socket.send_fds(conn, [b"mc"], [fd.value])
+                conn.close()
+            srv.close()
+            os.unlink(path)
+            os.close(fd.value)
+        else:
+            cli = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+            cli.connect(path)
+            _msg, fds, _flags, _addr = socket.recv_fds(cli, 16, 1)
+            cli.close()
+            ok = len(fds) == 1 and lib.b2_nvls_import(ctx, fds[0], rounded_bytes) == 0
+            if fds:
+                os.close(fds[0])
+        # 2. every device joins, then every rank binds its memory and maps both views
+        ok = ok and lib.b2_nvls_add_device(ctx) == 0
+        if not agree(ok):
+            self.nvls_error = lib.b2_last_error().decode(errors="replace")
+            return False
+        ok = lib.b2_nvls_bind(ctx) == 0
+        if not ok:
+            self.nvls_error = lib.b2_last_error().decode(errors="replace")
+        if not agree(ok):
+            return False
+        self.nvls = True
+        return True
+
+    def allreduce_nvls_(self, tensor: torch.Tensor, scale: float = 1.0, *,
+                        stream: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
+        """In place, reduced inside the NVSwitch (identical on all ranks; fp32-rounding-equal to
+        the rank-ordered sum)."""
+        if not self.nvls:
+            raise RuntimeError("allreduce_nvls_: enable_nvls() has not succeeded")
+        if tensor.device != self.device or tensor.dtype != torch.float32 or not tensor.is_contiguous():
+            raise ValueError("allreduce_nvls_: contiguous fp32 tensor on the communicator's device required")
+        s = (stream or torch.cuda.current_stream(self.device)).cuda_stream
+        _lib.check(self._lib.b2_allreduce_nvls(self._ctx, tensor.data_ptr(), tensor.numel(), float(scale), s))
+        _lib.count_launch()
         return tensor
 
     def check(self) -> None:

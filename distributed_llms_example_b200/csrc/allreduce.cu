@@ -27,87 +27,10 @@
 #include <cstring>
 #include <vector>
 
-#include "common.cuh"
+#include "allreduce_shared.cuh"
 
 namespace b2 {
 
-constexpr int kArThreads = 512;
-constexpr int kArMaxBlocks = 128;                                        // rows of the flag pad
-constexpr size_t kPadBytes = 16384;                                      // flags + status word
-constexpr size_t kStatusOff = kArMaxBlocks * B2_MAX_WORLD * 4;           // after the flags
-constexpr size_t kGateOff = kStatusOff + 256;                            // B2_MAX_WORLD gate flags
-static_assert(kGateOff + B2_MAX_WORLD * 4 <= kPadBytes, "flag pad too small");
-
-struct RankView {
-  float* buf;                        // this rank's bucket, reduced in place
-  char* stage[B2_MAX_WORLD];         // staging half of every rank, as mapped by this rank
-  uint32_t* flags[B2_MAX_WORLD];     // flag pad of every rank, as mapped by this rank
-  uint32_t* status;                  // this rank's sticky timeout word
-  int rank;
-};
-
-template <int NV>
-struct ArArgs {
-  RankView v[NV];
-};
-
-__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
-  uint32_t v;
-  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void fence_acquire_sys() {
-  asm volatile("fence.acq_rel.sys;" ::: "memory");
-}
-// Peer (or own) staging written by another GPU during this kernel: relaxed system-scope load,
-// never the non-coherent path.
-__device__ __forceinline__ uint4 ld_peer16(const void* p) {
-  uint4 r;
-  asm volatile("ld.relaxed.sys.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-               : "l"(p)
-               : "memory");
-  return r;
-}
-__device__ __forceinline__ unsigned long long globaltimer_ns() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-  return t;
-}
-
-// All CTAs with the same blockIdx.x on all ranks meet here. Data written by any thread of
-// the CTA before the call is visible to the peers' CTAs after it (bar.sync orders the CTA's
-// writes before the releasing store; the peer's acquiring load orders its reads after).
-template <int W>
-__device__ __forceinline__ void cross_barrier(const RankView& v, uint32_t epoch,
-                                              unsigned long long timeout_ns) {
-  __syncthreads();
-  if (W > 1 && threadIdx.x < W) {
-    const int peer = threadIdx.x;
-    st_release_sys(v.flags[peer] + blockIdx.x * B2_MAX_WORLD + v.rank, epoch);
-    const uint32_t* mine = v.flags[v.rank] + blockIdx.x * B2_MAX_WORLD + peer;
-    const unsigned long long t0 = globaltimer_ns();
-    unsigned spins = 0;
-    // poll with relaxed loads (cheap), then one acquire fence once the flag has arrived
-    while ((int)(ld_relaxed_sys(mine) - epoch) < 0) {
-      if ((++spins & 1023u) == 0 && globaltimer_ns() - t0 > timeout_ns) {
-        atomicExch(v.status, 1u);  // sticky; b2_comm_status reports B2_ERR_TIMEOUT
-        break;
-      }
-    }
-    fence_acquire_sys();
-  }
-  __syncthreads();
-}
-
-// One tiny CTA per rank that meets its peers BEFORE the wide kernel is launched behind it on the
-// same stream: ranks reach a bucket at different times (the training step is host-bound more
-// often than not), and waiting for a late peer should cost one SM, not the 64 the data
-// kernel occupies. After the gate every rank's bucket is complete and the data kernels start
-// within launch skew of each other.
 template <int W>
 __global__ void __launch_bounds__(32, 1)
 gate_kernel(const __grid_constant__ ArArgs<1> args, uint32_t epoch, unsigned long long timeout_ns) {
@@ -130,83 +53,6 @@ gate_kernel(const __grid_constant__ ArArgs<1> args, uint32_t epoch, unsigned lon
   }
 }
 
-template <bool BF16W>
-struct Wire;
-template <>
-struct Wire<false> {
-  static constexpr int kElems = 4;  // elements per 16-byte staged pack
-  static __device__ __forceinline__ uint4 load_scaled(const float* buf, long long pack, float scale) {
-    uint4 u = ld_stream16(buf + pack * 4);
-    u.x = __float_as_uint(__fmul_rn(__uint_as_float(u.x), scale));
-    u.y = __float_as_uint(__fmul_rn(__uint_as_float(u.y), scale));
-    u.z = __float_as_uint(__fmul_rn(__uint_as_float(u.z), scale));
-    u.w = __float_as_uint(__fmul_rn(__uint_as_float(u.w), scale));
-    return u;
-  }
-  static __device__ __forceinline__ void to_f(uint4 u, float* x) {
-    x[0] = __uint_as_float(u.x); x[1] = __uint_as_float(u.y);
-    x[2] = __uint_as_float(u.z); x[3] = __uint_as_float(u.w);
-  }
-  static __device__ __forceinline__ uint4 from_f(const float* x) {
-    return make_uint4(__float_as_uint(x[0]), __float_as_uint(x[1]), __float_as_uint(x[2]),
-                      __float_as_uint(x[3]));
-  }
-  static __device__ __forceinline__ void store_buf(float* buf, long long pack, uint4 staged) {
-    *reinterpret_cast<uint4*>(buf + pack * 4) = staged;
-  }
-  static __device__ __forceinline__ float stage1(const float* buf, long long e, float scale) {
-    return __fmul_rn(buf[e], scale);
-  }
-  // tail elements (numel % kElems) live after the last whole pack of the staging half
-  static __device__ __forceinline__ void tail_store(char* base, int i, float f) {
-    reinterpret_cast<float*>(base)[i] = f;
-  }
-  static __device__ __forceinline__ float tail_load(const char* base, int i) {
-    return reinterpret_cast<const volatile float*>(base)[i];
-  }
-  static __device__ __forceinline__ float round_wire(float f) { return f; }
-};
-template <>
-struct Wire<true> {
-  static constexpr int kElems = 8;
-  static __device__ __forceinline__ uint4 load_scaled(const float* buf, long long pack, float scale) {
-    const uint4 a = ld_stream16(buf + pack * 8), b = ld_stream16(buf + pack * 8 + 4);
-    return make_uint4(
-        pack_bf16(__uint_as_float(a.x) * scale, __uint_as_float(a.y) * scale),
-        pack_bf16(__uint_as_float(a.z) * scale, __uint_as_float(a.w) * scale),
-        pack_bf16(__uint_as_float(b.x) * scale, __uint_as_float(b.y) * scale),
-        pack_bf16(__uint_as_float(b.z) * scale, __uint_as_float(b.w) * scale));
-  }
-  static __device__ __forceinline__ void to_f(uint4 u, float* x) {
-    x[0] = bf16lo(u.x); x[1] = bf16hi(u.x); x[2] = bf16lo(u.y); x[3] = bf16hi(u.y);
-    x[4] = bf16lo(u.z); x[5] = bf16hi(u.z); x[6] = bf16lo(u.w); x[7] = bf16hi(u.w);
-  }
-  static __device__ __forceinline__ uint4 from_f(const float* x) {
-    return make_uint4(pack_bf16(x[0], x[1]), pack_bf16(x[2], x[3]), pack_bf16(x[4], x[5]),
-                      pack_bf16(x[6], x[7]));
-  }
-  static __device__ __forceinline__ void store_buf(float* buf, long long pack, uint4 staged) {
-    float x[8];
-    to_f(staged, x);
-    uint4* o = reinterpret_cast<uint4*>(buf + pack * 8);
-    o[0] = make_uint4(__float_as_uint(x[0]), __float_as_uint(x[1]), __float_as_uint(x[2]), __float_as_uint(x[3]));
-    o[1] = make_uint4(__float_as_uint(x[4]), __float_as_uint(x[5]), __float_as_uint(x[6]), __float_as_uint(x[7]));
-  }
-  static __device__ __forceinline__ float stage1(const float* buf, long long e, float scale) {
-    return round_wire(buf[e] * scale);
-  }
-  static __device__ __forceinline__ void tail_store(char* base, int i, float f) {
-    reinterpret_cast<unsigned short*>(base)[i] = (unsigned short)(__float_as_uint(round_wire(f)) >> 16);
-  }
-  static __device__ __forceinline__ float tail_load(const char* base, int i) {
-    return __uint_as_float((uint32_t) reinterpret_cast<const volatile unsigned short*>(base)[i] << 16);
-  }
-  static __device__ __forceinline__ float round_wire(float f) {
-    return __bfloat162float(__float2bfloat16_rn(f));
-  }
-};
-
-// Sum of pack `i` over all ranks, rank order 0..W-1, fp32 adds (no fma, no reassociation).
 template <int W, bool BF16W>
 __device__ __forceinline__ void reduce_packs(const RankView& v, long long i, float* acc) {
   using Wr = Wire<BF16W>;
@@ -589,57 +435,13 @@ static KernelFn pick_inplace_kernel(int world) {
   return nullptr;
 }
 
-static long long env_ll(const char* name, long long dflt) {
-  const char* s = std::getenv(name);
-  if (!s || !*s) return dflt;
-  char* end = nullptr;
-  long long v = std::strtoll(s, &end, 10);
-  return (end && *end == 0) ? v : dflt;
-}
-
-// One-shot moves (W-1)*S inbound per rank and needs one barrier; two-shot moves
-// 2(W-1)/W*S and needs two. At W=2 the bytes are equal, so one-shot always wins.
 static int pick_algo(int world, long long bytes) {
   if (world <= 2) return B2_ALGO_ONE_SHOT;
   const long long thresh = env_ll("B2_AR_ONE_SHOT_MAX_BYTES", world == 4 ? (4ll << 20) : (1ll << 20));
   return bytes <= thresh ? B2_ALGO_ONE_SHOT : B2_ALGO_TWO_SHOT;
 }
 
-static int pick_blocks(long long npack, int max_blocks) {
-  // ~2 packs-of-4-unroll per thread before adding a CTA; small buckets stay on few CTAs so
-  // the barrier is cheap and the backward GEMMs keep their SMs.
-  long long nb = (npack + (long long)kArThreads * 8 - 1) / ((long long)kArThreads * 8);
-  if (nb < 1) nb = 1;
-  if (nb > max_blocks) nb = max_blocks;
-  return (int)nb;
-}
-
 }  // namespace b2
-
-struct b2_opened_handle {  // one cudaIpcOpenMemHandle per distinct peer allocation
-  int peer;
-  unsigned char handle[B2_IPC_HANDLE_BYTES];
-  char* base;
-};
-
-struct b2_registration {
-  bool live = false;
-  size_t bytes = 0;
-  char* ptr[B2_MAX_WORLD] = {nullptr};  // the registered buffer of every rank, as mapped here
-};
-
-struct b2_comm {
-  std::vector<b2_opened_handle> peer_allocs;
-  std::vector<b2_registration> regs;
-  int rank = 0, world = 1, device = 0;
-  size_t half_bytes = 0;
-  char* base[B2_MAX_WORLD] = {nullptr};  // mapped symmetric allocation of every rank
-  bool opened = false;
-  uint32_t epoch = 1;
-  int parity = 0;
-  int max_blocks = 96;
-  unsigned long long timeout_ns = 30ull * 1000000000ull;
-};
 
 extern "C" int b2_comm_create(int rank, int world, size_t staging_bytes, b2_comm** out) {
   using namespace b2;
@@ -871,6 +673,28 @@ extern "C" int b2_allreduce_registered(b2_comm* c, int reg_id, int64_t numel, fl
   return B2_OK;
 }
 
+// Whether the current device can join an NVLink multicast object (NVLS: multimem.ld_reduce /
+// multimem.st). Information only in this round: the in-switch reduction path is the next step.
+extern "C" int b2_nvls_supported(int* supported_out) {
+  using namespace b2;
+  B2_REQUIRE(supported_out, "nvls_supported: null pointer");
+  *supported_out = 0;
+  int dev = 0;
+  B2_CUDA_CHECK(cudaGetDevice(&dev));
+  typedef int (*GetAttr)(int*, int, int);
+  void* f = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  B2_CUDA_CHECK(cudaGetDriverEntryPoint("cuDeviceGetAttribute", &f, cudaEnableDefault, &q));
+  if (!f || q != cudaDriverEntryPointSuccess)
+    return fail(B2_ERR_CUDA, "nvls_supported: cuDeviceGetAttribute is not available");
+  int v = 0;
+  const int kMulticastSupported = 132;  // CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED
+  const int rc = ((GetAttr)f)(&v, kMulticastSupported, dev);
+  if (rc != 0) return fail(B2_ERR_CUDA, "nvls_supported: cuDeviceGetAttribute failed with CUresult %d", rc);
+  *supported_out = v;
+  return B2_OK;
+}
+
 extern "C" int b2_comm_status(b2_comm* c) {
   using namespace b2;
   B2_REQUIRE(c, "comm_status: null comm");
@@ -884,6 +708,7 @@ extern "C" int b2_comm_status(b2_comm* c) {
 extern "C" int b2_comm_destroy(b2_comm* c) {
   using namespace b2;
   if (!c) return B2_OK;
+  b2_nvls_release(c);
   for (auto& h : c->peer_allocs) cudaIpcCloseMemHandle(h.base);
   for (int r = 0; r < c->world; ++r) {
     if (!c->base[r]) continue;

@@ -1,0 +1,359 @@
+// Gradient all-reduce with in-switch reduction (NVLink SHARP / NVLS), SURVEY.md 8f row 3.
+//
+// Plain peer-to-peer all-reduce has to move 2(W-1)/W*S through every GPU's NVLink port in EACH
+// direction. With a multicast object bound to one buffer per GPU, `multimem.ld_reduce` asks the
+// NVSwitch for "the sum over all GPUs of the word at this offset" and `multimem.st` stores one
+// word into every GPU's buffer: the owner of a slice pulls S/W reduced bytes and pushes S/W,
+// and each port carries ~S per direction instead of 1.75*S at W=8.
+//
+//   one kernel per call (all W ranks):
+//     copy-in   bucket -> this rank's multicast-bound buffer (unicast mapping), x scale
+//     barrier   per-CTA flags in the communicator's IPC-mapped pad (allreduce.cu)
+//     reduce    slice owner: v = multimem.ld_reduce.add.f32x4 [mc + i]; multimem.st [mc + i], v
+//     barrier
+//     copy-out  this rank's buffer -> bucket
+//
+// Every element is reduced exactly once (by its slice owner, inside the switch) and broadcast,
+// so all ranks hold bit-identical results; the order in which the switch adds the W values is
+// the hardware's, so against the rank-ordered oracle this path is equal to fp32 rounding
+// (<= 1e-6 relative), not bit for bit - the same standard as NCCL's own ring/tree/NVLS orders.
+// A single buffer suffices across consecutive calls: a rank's next copy-in only overwrites its
+// own buffer after it passed the second barrier of this call, which every peer enters only after
+// finishing its switch reads.
+//
+// Set-up (host, all through driver entry points resolved at run time, no libcuda link):
+//   rank 0: cuMulticastCreate -> POSIX fd, passed to the other ranks by the host (SCM_RIGHTS);
+//   all: cuMulticastAddDevice; barrier; cuMemCreate + cuMulticastBindMem; map unicast and
+//   multicast virtual ranges.
+#include <cuda.h>
+#include <unistd.h>
+
+#include <cstdlib>
+#include <cstring>
+
+#include "allreduce_shared.cuh"
+
+namespace b2 {
+
+struct Drv {
+  CUresult (*memGetAllocationGranularity)(size_t*, const CUmemAllocationProp*, CUmemAllocationGranularity_flags);
+  CUresult (*memCreate)(CUmemGenericAllocationHandle*, size_t, const CUmemAllocationProp*, unsigned long long);
+  CUresult (*memRelease)(CUmemGenericAllocationHandle);
+  CUresult (*memAddressReserve)(CUdeviceptr*, size_t, size_t, CUdeviceptr, unsigned long long);
+  CUresult (*memAddressFree)(CUdeviceptr, size_t);
+  CUresult (*memMap)(CUdeviceptr, size_t, size_t, CUmemGenericAllocationHandle, unsigned long long);
+  CUresult (*memUnmap)(CUdeviceptr, size_t);
+  CUresult (*memSetAccess)(CUdeviceptr, size_t, const CUmemAccessDesc*, size_t);
+  CUresult (*memExportToShareableHandle)(void*, CUmemGenericAllocationHandle, CUmemAllocationHandleType, unsigned long long);
+  CUresult (*memImportFromShareableHandle)(CUmemGenericAllocationHandle*, void*, CUmemAllocationHandleType);
+  CUresult (*multicastCreate)(CUmemGenericAllocationHandle*, const CUmulticastObjectProp*);
+  CUresult (*multicastAddDevice)(CUmemGenericAllocationHandle, CUdevice);
+  CUresult (*multicastBindMem)(CUmemGenericAllocationHandle, size_t, CUmemGenericAllocationHandle, size_t, size_t, unsigned long long);
+  CUresult (*multicastGetGranularity)(size_t*, const CUmulticastObjectProp*, CUmulticastGranularity_flags);
+  CUresult (*multicastUnbind)(CUmemGenericAllocationHandle, CUdevice, size_t, size_t);
+  CUresult (*deviceGet)(CUdevice*, int);
+  bool ok = false;
+};
+
+static int load_one(const char* name, void** out) {
+  cudaDriverEntryPointQueryResult q;
+  cudaError_t e = cudaGetDriverEntryPoint(name, out, cudaEnableDefault, &q);
+  if (e != cudaSuccess || q != cudaDriverEntryPointSuccess || !*out)
+    return fail(B2_ERR_CUDA, "nvls: driver entry point %s is not available", name);
+  return B2_OK;
+}
+
+static int drv(Drv** out) {
+  static Drv d;
+  if (!d.ok) {
+#define B2_LOAD(field, name)                                  \
+  {                                                           \
+    int rc = load_one(name, (void**)&d.field);                \
+    if (rc != B2_OK) return rc;                               \
+  }
+    B2_LOAD(memGetAllocationGranularity, "cuMemGetAllocationGranularity")
+    B2_LOAD(memCreate, "cuMemCreate")
+    B2_LOAD(memRelease, "cuMemRelease")
+    B2_LOAD(memAddressReserve, "cuMemAddressReserve")
+    B2_LOAD(memAddressFree, "cuMemAddressFree")
+    B2_LOAD(memMap, "cuMemMap")
+    B2_LOAD(memUnmap, "cuMemUnmap")
+    B2_LOAD(memSetAccess, "cuMemSetAccess")
+    B2_LOAD(memExportToShareableHandle, "cuMemExportToShareableHandle")
+    B2_LOAD(memImportFromShareableHandle, "cuMemImportFromShareableHandle")
+    B2_LOAD(multicastCreate, "cuMulticastCreate")
+    B2_LOAD(multicastAddDevice, "cuMulticastAddDevice")
+    B2_LOAD(multicastBindMem, "cuMulticastBindMem")
+    B2_LOAD(multicastGetGranularity, "cuMulticastGetGranularity")
+    B2_LOAD(multicastUnbind, "cuMulticastUnbind")
+    B2_LOAD(deviceGet, "cuDeviceGet")
+#undef B2_LOAD
+    d.ok = true;
+  }
+  *out = &d;
+  return B2_OK;
+}
+
+#define B2_DRV_CHECK(expr)                                                                    \
+  do {                                                                                        \
+    CUresult _r = (expr);                                                                     \
+    if (_r != CUDA_SUCCESS)                                                                   \
+      return ::b2::fail(B2_ERR_CUDA, "%s failed with CUresult %d (%s:%d)", #expr, (int)_r,    \
+                        __FILE__, __LINE__);                                                  \
+  } while (0)
+
+// ---- device side ----------------------------------------------------------------------------
+__device__ __forceinline__ uint4 multimem_ld_reduce_f32x4(const void* mc) {
+  uint4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(mc)
+               : "memory");
+  return r;
+}
+__device__ __forceinline__ void multimem_st_f32x4(void* mc, uint4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "r"(v.x),
+               "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ float multimem_ld_reduce_f32(const void* mc) {
+  float r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.f32 %0, [%1];" : "=f"(r) : "l"(mc) : "memory");
+  return r;
+}
+__device__ __forceinline__ void multimem_st_f32(void* mc, float v) {
+  asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(mc), "f"(v) : "memory");
+}
+
+struct NvlsArgs {
+  RankView v;   // buf = bucket; flags[] = communicator pads; stage[] unused
+  char* uc;     // this rank's multicast-bound buffer, unicast mapping
+  char* mc;     // the multicast mapping of all ranks' buffers
+};
+
+template <int W>
+__global__ void __launch_bounds__(kArThreads, 1)
+allreduce_nvls_kernel(const __grid_constant__ NvlsArgs a, long long numel, float scale, uint32_t epoch,
+                      unsigned long long timeout_ns) {
+  const RankView& v = a.v;
+  const int rank = v.rank;
+  const int nb = gridDim.x, b = blockIdx.x, tid = threadIdx.x;
+  const long long npack = numel / 4;
+  const long long tail0 = npack * 4;
+  float* __restrict__ buf = v.buf;
+  const long long Q = (npack + W - 1) / W;
+  const long long q = (Q + nb - 1) / nb;
+  constexpr int U = 4;
+
+  // copy-in: this CTA stages its sub-range of every slice (the peer CTA with the same index
+  // is the one whose switch read will touch it after the per-CTA barrier)
+#pragma unroll 1
+  for (int s = 0; s < W; ++s) {
+    const long long slo = min((long long)s * Q, npack), shi = min(slo + Q, npack);
+    const long long lo = min(slo + (long long)b * q, shi), hi = min(lo + q, shi);
+    long long i = lo + tid;
+    for (; i + (U - 1) * kArThreads < hi; i += U * kArThreads) {
+      uint4 t[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) t[u] = Wire<false>::load_scaled(buf, i + u * kArThreads, scale);
+#pragma unroll
+      for (int u = 0; u < U; ++u) *reinterpret_cast<uint4*>(a.uc + (i + u * kArThreads) * 16) = t[u];
+    }
+    for (; i < hi; i += kArThreads)
+      *reinterpret_cast<uint4*>(a.uc + i * 16) = Wire<false>::load_scaled(buf, i, scale);
+  }
+  if (b == 0 && tid < numel - tail0)
+    reinterpret_cast<float*>(a.uc + tail0 * 4)[tid] = __fmul_rn(buf[tail0 + tid], scale);
+  __threadfence_system();
+  cross_barrier<W>(v, epoch, timeout_ns);
+
+  // in-switch reduce + broadcast of my slice
+  {
+    const long long slo = min((long long)rank * Q, npack), shi = min(slo + Q, npack);
+    const long long lo = min(slo + (long long)b * q, shi), hi = min(lo + q, shi);
+    long long i = lo + tid;
+    for (; i + (U - 1) * kArThreads < hi; i += U * kArThreads) {
+      uint4 t[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) t[u] = multimem_ld_reduce_f32x4(a.mc + (i + u * kArThreads) * 16);
+#pragma unroll
+      for (int u = 0; u < U; ++u) multimem_st_f32x4(a.mc + (i + u * kArThreads) * 16, t[u]);
+    }
+    for (; i < hi; i += kArThreads) multimem_st_f32x4(a.mc + i * 16, multimem_ld_reduce_f32x4(a.mc + i * 16));
+    if (rank == 0 && b == 0 && tid < numel - tail0) {
+      char* p = a.mc + tail0 * 4 + (size_t)tid * 4;
+      multimem_st_f32(p, multimem_ld_reduce_f32(p));
+    }
+  }
+  __threadfence_system();
+  cross_barrier<W>(v, epoch + 1, timeout_ns);
+
+  // copy-out (system-scope loads: peers wrote this memory through the switch)
+#pragma unroll 1
+  for (int s = 0; s < W; ++s) {
+    const long long slo = min((long long)s * Q, npack), shi = min(slo + Q, npack);
+    const long long lo = min(slo + (long long)b * q, shi), hi = min(lo + q, shi);
+    long long i = lo + tid;
+    for (; i + (U - 1) * kArThreads < hi; i += U * kArThreads) {
+      uint4 t[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) t[u] = ld_peer16(a.uc + (i + u * kArThreads) * 16);
+#pragma unroll
+      for (int u = 0; u < U; ++u) *reinterpret_cast<uint4*>(buf + (i + u * kArThreads) * 4) = t[u];
+    }
+    for (; i < hi; i += kArThreads) *reinterpret_cast<uint4*>(buf + i * 4) = ld_peer16(a.uc + i * 16);
+  }
+  if (b == 0 && tid < numel - tail0)
+    buf[tail0 + tid] = Wire<false>::tail_load(a.uc + tail0 * 4, tid);
+}
+
+}  // namespace b2
+
+using b2::Drv;
+
+extern "C" int b2_nvls_create(b2_comm* c, size_t bytes, int* fd_out, size_t* rounded_out) {
+  using namespace b2;
+  B2_REQUIRE(c && fd_out && rounded_out, "nvls_create: null pointer");
+  B2_REQUIRE(c->rank == 0, "nvls_create: only rank 0 creates the multicast object");
+  B2_REQUIRE(c->world >= 2, "nvls_create: needs at least two ranks");
+  Drv* d;
+  int rc = drv(&d);
+  if (rc != B2_OK) return rc;
+  CUmulticastObjectProp prop;
+  std::memset(&prop, 0, sizeof(prop));
+  prop.numDevices = (unsigned)c->world;
+  prop.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+  prop.size = bytes;
+  size_t gran = 0;
+  B2_DRV_CHECK(d->multicastGetGranularity(&gran, &prop, CU_MULTICAST_GRANULARITY_RECOMMENDED));
+  if (gran == 0) return fail(B2_ERR_CUDA, "nvls_create: zero multicast granularity");
+  prop.size = (bytes + gran - 1) / gran * gran;
+  B2_DRV_CHECK(d->multicastCreate(&c->nvls.mc, &prop));
+  int fd = -1;
+  B2_DRV_CHECK(d->memExportToShareableHandle(&fd, c->nvls.mc, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0));
+  c->nvls.bytes = prop.size;
+  c->nvls.have_mc = true;
+  *fd_out = fd;
+  *rounded_out = prop.size;
+  return B2_OK;
+}
+
+extern "C" int b2_nvls_import(b2_comm* c, int fd, size_t rounded_bytes) {
+  using namespace b2;
+  B2_REQUIRE(c && fd >= 0, "nvls_import: bad arguments");
+  B2_REQUIRE(c->rank != 0, "nvls_import: rank 0 already owns the object");
+  Drv* d;
+  int rc = drv(&d);
+  if (rc != B2_OK) return rc;
+  B2_DRV_CHECK(d->memImportFromShareableHandle(&c->nvls.mc, (void*)(uintptr_t)fd,
+                                               CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR));
+  c->nvls.bytes = rounded_bytes;
+  c->nvls.have_mc = true;
+  return B2_OK;
+}
+
+extern "C" int b2_nvls_add_device(b2_comm* c) {
+  using namespace b2;
+  B2_REQUIRE(c && c->nvls.have_mc, "nvls_add_device: no multicast object yet");
+  Drv* d;
+  int rc = drv(&d);
+  if (rc != B2_OK) return rc;
+  CUdevice dev;
+  B2_DRV_CHECK(d->deviceGet(&dev, c->device));
+  B2_DRV_CHECK(d->multicastAddDevice(c->nvls.mc, dev));
+  return B2_OK;
+}
+
+extern "C" int b2_nvls_bind(b2_comm* c) {
+  using namespace b2;
+  B2_REQUIRE(c && c->nvls.have_mc, "nvls_bind: no multicast object yet");
+  Drv* d;
+  int rc = drv(&d);
+  if (rc != B2_OK) return rc;
+  b2_nvls& n = c->nvls;
+  CUmemAllocationProp prop;
+  std::memset(&prop, 0, sizeof(prop));
+  prop.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+  prop.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+  prop.location.id = c->device;
+  prop.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+  size_t gran = 0;
+  B2_DRV_CHECK(d->memGetAllocationGranularity(&gran, &prop, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED));
+  if (gran == 0 || n.bytes % gran != 0)
+    return fail(B2_ERR_CUDA, "nvls_bind: size %zu is not a multiple of the allocation granularity %zu", n.bytes, gran);
+  B2_DRV_CHECK(d->memCreate(&n.mem, n.bytes, &prop, 0));
+  B2_DRV_CHECK(d->multicastBindMem(n.mc, 0, n.mem, 0, n.bytes, 0));
+  CUmemAccessDesc acc;
+  std::memset(&acc, 0, sizeof(acc));
+  acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+  acc.location.id = c->device;
+  acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+  B2_DRV_CHECK(d->memAddressReserve(&n.uc_va, n.bytes, gran, 0, 0));
+  B2_DRV_CHECK(d->memMap(n.uc_va, n.bytes, 0, n.mem, 0));
+  B2_DRV_CHECK(d->memSetAccess(n.uc_va, n.bytes, &acc, 1));
+  B2_DRV_CHECK(d->memAddressReserve(&n.mc_va, n.bytes, gran, 0, 0));
+  B2_DRV_CHECK(d->memMap(n.mc_va, n.bytes, 0, n.mc, 0));
+  B2_DRV_CHECK(d->memSetAccess(n.mc_va, n.bytes, &acc, 1));
+  B2_CUDA_CHECK(cudaMemset((void*)n.uc_va, 0, n.bytes));
+  n.ready = true;
+  return B2_OK;
+}
+
+extern "C" int b2_allreduce_nvls(b2_comm* c, void* buf, int64_t numel, float scale, b2_stream_t stream) {
+  using namespace b2;
+  B2_REQUIRE(c, "allreduce_nvls: null comm");
+  if (!c->nvls.ready) return fail(B2_ERR_STATE, "allreduce_nvls: b2_nvls_bind has not completed on this rank");
+  B2_REQUIRE(numel >= 0, "allreduce_nvls: negative numel");
+  if (numel == 0) return B2_OK;
+  B2_REQUIRE(buf && (((uintptr_t)buf) & 15) == 0, "allreduce_nvls: buffer null or not 16-byte aligned");
+  const long long cap = (long long)((c->nvls.bytes - 64) / 4 / 4 * 4);
+  for (long long off = 0; off < numel; off += cap) {
+    const long long n = (numel - off < cap) ? (numel - off) : cap;
+    NvlsArgs a;
+    a.v.buf = (float*)buf + off;
+    a.v.rank = c->rank;
+    for (int r = 0; r < B2_MAX_WORLD; ++r) {
+      const int k = r < c->world ? r : c->rank;
+      a.v.stage[r] = nullptr;
+      a.v.flags[r] = (uint32_t*)c->base[k];
+    }
+    a.v.status = (uint32_t*)(c->base[c->rank] + kStatusOff);
+    a.uc = (char*)c->nvls.uc_va;
+    a.mc = (char*)c->nvls.mc_va;
+    const void* fn = c->world == 2 ? (const void*)allreduce_nvls_kernel<2>
+                   : c->world == 4 ? (const void*)allreduce_nvls_kernel<4>
+                                   : (const void*)allreduce_nvls_kernel<8>;
+    // the two local copy passes are HBM-bound: give them every row of the flag pad
+    const int nb = pick_blocks(n / 4 / 2, kArMaxBlocks);
+    long long n_arg = n;
+    float scale_arg = scale;
+    uint32_t epoch = c->epoch;
+    unsigned long long to = c->timeout_ns;
+    void* kargs[] = {&a, &n_arg, &scale_arg, &epoch, &to};
+    B2_CUDA_CHECK(cudaLaunchKernel(fn, dim3(nb), dim3(kArThreads), kargs, 0, (cudaStream_t)stream));
+    c->epoch += 2;
+  }
+  return B2_OK;
+}
+
+// called by b2_comm_destroy
+int b2_nvls_release(b2_comm* c) {
+  using namespace b2;
+  b2_nvls& n = c->nvls;
+  if (!n.have_mc) return B2_OK;
+  Drv* d;
+  if (drv(&d) != B2_OK) return B2_OK;
+  if (n.ready) {
+    CUdevice dev;
+    d->deviceGet(&dev, c->device);
+    d->memUnmap(n.mc_va, n.bytes);
+    d->memAddressFree(n.mc_va, n.bytes);
+    d->multicastUnbind(n.mc, dev, 0, n.bytes);
+    d->memUnmap(n.uc_va, n.bytes);
+    d->memAddressFree(n.uc_va, n.bytes);
+    d->memRelease(n.mem);
+  }
+  d->memRelease(n.mc);
+  n = b2_nvls();
+  return B2_OK;
+}

@@ -217,6 +217,22 @@ int b2_comm_register(b2_comm* c, void* local_ptr, size_t bytes, const void* hand
 int b2_comm_unregister(b2_comm* c, int reg_id);
 int b2_allreduce_registered(b2_comm* c, int reg_id, int64_t numel, float scale,
                             b2_stream_t stream);
+/* In-switch reduction (NVLink SHARP / NVLS): the same mean all-reduce as
+ * b2_allreduce, with the sum formed inside the NVSwitch (multimem.ld_reduce / multimem.st) so
+ * that each NVLink port carries ~S bytes per direction instead of 2(W-1)/W*S. Results are
+ * bit-identical on every rank; against the rank-ordered sum they agree to fp32 rounding (the
+ * switch's add order), the same standard as NCCL's ring/tree/NVLS orders. World 2, 4 or 8.
+ * Set-up, after b2_comm_open_peers, in this order on every rank (host barriers between steps):
+ *   rank 0: b2_nvls_create(bytes) -> POSIX fd + rounded size; the host passes the fd to the
+ *           other ranks (SCM_RIGHTS over a Unix socket), which call b2_nvls_import(fd, rounded);
+ *   all:    b2_nvls_add_device; <barrier>; b2_nvls_bind; <barrier>.
+ * b2_nvls_supported: 1 when the current device can join a multicast object. */
+int b2_nvls_supported(int* supported_out);
+int b2_nvls_create(b2_comm* c, size_t bytes, int* fd_out, size_t* rounded_out);
+int b2_nvls_import(b2_comm* c, int fd, size_t rounded_bytes);
+int b2_nvls_add_device(b2_comm* c);
+int b2_nvls_bind(b2_comm* c);
+int b2_allreduce_nvls(b2_comm* c, void* buf, int64_t numel, float scale, b2_stream_t stream);
 /* 0, or B2_ERR_TIMEOUT once a kernel gave up waiting for a peer (sticky). */
 int b2_comm_status(b2_comm* c);
 int b2_comm_destroy(b2_comm* c);

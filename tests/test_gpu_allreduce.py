@@ -140,6 +140,21 @@ def _worker(rank, world, port, q):
                 torch.cuda.synchronize()
                 results[(n, "registered", rep)] = bool(np.array_equal(x.cpu().numpy(), O.allreduce_mean(bufs)))
             comm.unregister(reg)
+        # in-switch reduction (NVLS): identical on every rank, fp32-rounding-equal to the oracle
+        nvls_ok = comm.enable_nvls(8 << 20)
+        results[("nvls_enabled", comm.nvls_error)] = bool(nvls_ok)
+        if nvls_ok:
+            for n in (3, 4100, 1 << 20, (8 << 20) // 4 * 2 + 9):  # the last one is chunked
+                bufs = allreduce_inputs(world, n, 700 + n % 89)
+                x = torch.from_numpy(bufs[rank].copy()).cuda()
+                comm.allreduce_nvls_(x, 1.0 / world)
+                torch.cuda.synchronize()
+                ref = O.allreduce_mean(bufs)
+                close = bool(np.allclose(x.cpu().numpy(), ref, rtol=1e-6, atol=1e-9))
+                parts = [torch.empty_like(x) for _ in range(world)]
+                dist.all_gather(parts, x)
+                results[(n, "nvls")] = close and all(torch.equal(parts[0], t) for t in parts)
+
         # train-task.py's average_gradients(model): one flat exchange, bit-exact vs the oracle, and
         # the second call reuses the registered flat buffer
         from distributed_llms_example_b200.comm import average_gradients
