@@ -232,7 +232,8 @@ def bench_allreduce(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     comm = P2PComm(staging_bytes=args.staging_mb << 20)
-    nvls = world > 1 and comm.enable_nvls()
+    nvls = world > 1 and comm.enable_nvls((int(sum(args.sizes_mb) * 1.1) + 256) << 20)
+    pool = comm.nvls_pool() if nvls else None
     if rank == 0:
         print(json.dumps({"nvls_enabled": bool(nvls), "nvls_error": comm.nvls_error}), flush=True)
 
@@ -266,7 +267,14 @@ def bench_allreduce(args):
                 ms = timed(lambda: comm.allreduce_(x, 1.0 / world, wire=wire, algo=algo), iters, args.warmup)
                 rows.append((f"b200_{wire}_{algo}", ms))
         if world > 1 and nvls:
-            rows.append(("b200_fp32_nvls", timed(lambda: comm.allreduce_nvls_(x, 1.0 / world), iters, args.warmup)))
+            rows.append(("b200_fp32_nvls_staged", timed(lambda: comm.allreduce_nvls_(x, 1.0 / world), iters, args.warmup)))
+            with torch.cuda.use_mem_pool(pool):
+                xp = torch.randn(n, device="cuda") * 1e-2
+            off = comm.nvls_offset(xp)
+            if off is not None:
+                rows.append(("b200_fp32_nvls_zero_copy",
+                             timed(lambda: comm.allreduce_nvls_inplace_(off, n, 1.0 / world), iters, args.warmup)))
+            del xp
         if world > 1:
             reg = comm.register(x)
             rows.append(("b200_fp32_zero_copy_inplace",

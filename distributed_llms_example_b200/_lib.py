@@ -66,6 +66,11 @@ SIGNATURES = {
     "b2_nvls_add_device": (C.c_int, [_vp]),
     "b2_nvls_bind": (C.c_int, [_vp]),
     "b2_allreduce_nvls": (C.c_int, [_vp, _vp, _i64, _f32, _vp]),
+    "b2_nvls_region": (C.c_int, [_vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+    "b2_nvls_pool_attach": (C.c_int, [_vp]),
+    "b2_pool_alloc": (_vp, [C.c_ssize_t, C.c_int, _vp]),
+    "b2_pool_free": (None, [_vp, C.c_ssize_t, C.c_int, _vp]),
+    "b2_allreduce_nvls_inplace": (C.c_int, [_vp, C.c_uint64, _i64, _f32, _vp]),
     "b2_comm_status": (C.c_int, [_vp]),
     "b2_comm_destroy": (C.c_int, [_vp]),
     "b2_allreduce_emulated_scratch_bytes": (_sz, [_i32, _i64]),

@@ -60,6 +60,8 @@ class P2PComm:
             raise ValueError(f"wire must be one of {list(_WIRE)}, algo one of {list(_ALGO)}")
         self.group, self.wire, self.algo = group, wire, algo
         self.nvls, self.nvls_error = False, ""
+        self._pool = self._pool_allocator = self._region = None
+        self.nvls_pool_bytes = 0
         self.device = torch.device("cuda", torch.cuda.current_device())
         if staging_bytes is None:
             staging_bytes = int(os.environ.get("B2_AR_STAGING_MB", "64")) << 20
@@ -203,6 +205,38 @@ class P2PComm:
         self.nvls = True
         return True
 
+    def nvls_pool(self) -> "torch.cuda.MemPool":
+        """A torch MemPool whose memory is the multicast-bound region: tensors allocated under
+        ``torch.cuda.use_mem_pool(pool)`` can be all-reduced by the switch in place."""
+        if not self.nvls:
+            raise RuntimeError("nvls_pool: enable_nvls() has not succeeded")
+        if self._pool is None:
+            _lib.check(self._lib.b2_nvls_pool_attach(self._ctx))
+            base, nbytes, pool_off = C.c_uint64(0), C.c_uint64(0), C.c_uint64(0)
+            _lib.check(self._lib.b2_nvls_region(self._ctx, C.byref(base), C.byref(nbytes), C.byref(pool_off)))
+            self._region = (base.value, nbytes.value)
+            self.nvls_pool_bytes = nbytes.value - pool_off.value
+            self._pool_allocator = torch.cuda.memory.CUDAPluggableAllocator(
+                str(_lib.lib_path()), "b2_pool_alloc", "b2_pool_free")
+            self._pool = torch.cuda.MemPool(self._pool_allocator.allocator())
+        return self._pool
+
+    def nvls_offset(self, tensor: torch.Tensor) -> Optional[int]:
+        """Byte offset of ``tensor`` inside the multicast-bound region, or None if it lives elsewhere."""
+        if self._region is None:
+            return None
+        base, nbytes = self._region
+        p = tensor.data_ptr()
+        if base <= p and p + tensor.numel() * tensor.element_size() <= base + nbytes:
+            return p - base
+        return None
+
+    def allreduce_nvls_inplace_(self, offset: int, numel: int, scale: float = 1.0, *,
+                                stream: Optional[torch.cuda.Stream] = None) -> None:
+        s = (stream or torch.cuda.current_stream(self.device)).cuda_stream
+        _lib.check(self._lib.b2_allreduce_nvls_inplace(self._ctx, offset, numel, float(scale), s))
+        _lib.count_launch(2)
+
     def allreduce_nvls_(self, tensor: torch.Tensor, scale: float = 1.0, *,
                         stream: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
         """In place, reduced inside the NVSwitch (identical on all ranks; fp32-rounding-equal to
@@ -275,11 +309,13 @@ class HookState:
         self.zero_copy = bool(zero_copy) and self.comm.world > 1 and self.comm.wire == "fp32"
         self.zero_copy_min_bytes = zero_copy_min_bytes
         self._last_seen: dict[int, tuple] = {}    # bucket index -> (data_ptr, numel) at its last call
-        self._registered: dict[int, tuple] = {}   # bucket index -> (data_ptr, numel, reg_id)
+        self._registered: dict[int, tuple] = {}   # bucket index -> (data_ptr, numel, reg_id | None, nvls offset | None)
+        self._c_allreduce_nvls_inplace = self.comm._lib.b2_allreduce_nvls_inplace
 
-    def registration_for(self, index: int, buf: torch.Tensor) -> Optional[int]:
+    def registration_for(self, index: int, buf: torch.Tensor) -> Optional[tuple]:
         """Collective while the bucket is unregistered: every rank contributes (stable?, handle,
-        offset); the bucket is registered only if it is stable everywhere."""
+        offset, nvls offset); the bucket is registered only if it is stable everywhere. Returns
+        (data_ptr, numel, ipc registration id | None, nvls offset | None) or None."""
         key = (buf.data_ptr(), buf.numel())
         reg = self._registered.get(index)
         if reg is not None:
@@ -287,22 +323,31 @@ class HookState:
                 raise RuntimeError(
                     f"DDP bucket {index} moved after it was registered for peer access "
                     f"({reg[:2]} -> {key}); rebuild the HookState (or set B2_AR_ZERO_COPY=0)")
-            return reg[2]
+            return reg
         if not self.zero_copy or buf.numel() * 4 < self.zero_copy_min_bytes:
             return None
         stable = self._last_seen.get(index) == key
         self._last_seen[index] = key
+        nvls_off = self.comm.nvls_offset(buf) if hasattr(self.comm, "nvls_offset") else None
         try:
-            mine = (stable,) + self.comm.export(buf)
+            mine = (stable,) + (self.comm.export(buf) if nvls_off is None else (b"", 0)) + (nvls_off,)
         except _lib.B2Error:
-            mine = (False, b"", 0)  # memory that cannot be exported (e.g. expandable segments)
+            mine = (False, b"", 0, None)  # memory that cannot be exported (e.g. expandable segments)
         votes: list = [None] * self.comm.world
         dist.all_gather_object(votes, mine, group=self.comm.group)
         if not all(v[0] for v in votes):
             return None
-        reg_id = self.comm.register(buf, peers=[(v[1], v[2]) for v in votes])
-        self._registered[index] = key + (reg_id,)
-        return reg_id
+        offs = {v[3] for v in votes}
+        if len(offs) == 1 and nvls_off is not None:
+            # the bucket sits at the same offset of the multicast-bound region on every rank:
+            # the switch reduces it in place, nothing to map
+            reg = key + (None, nvls_off)
+        elif None in offs and len(offs) == 1:
+            reg = key + (self.comm.register(buf, peers=[(v[1], v[2]) for v in votes]), None)
+        else:
+            return None  # mixed placement across ranks: stay on the staging path
+        self._registered[index] = reg
+        return reg
 
 
 def p2p_allreduce_hook(state: HookState, bucket: dist.GradBucket) -> torch.futures.Future[torch.Tensor]:
@@ -323,18 +368,19 @@ def p2p_allreduce_hook(state: HookState, bucket: dist.GradBucket) -> torch.futur
     producer = torch.cuda.current_stream(comm.device)
     state.event.record(producer)
     side.wait_event(state.event)
-    fast = state._registered.get(bucket.index()) if state.zero_copy else None
-    if fast is not None and fast[0] == buf.data_ptr() and fast[1] == buf.numel():
-        rc = state._c_allreduce_registered(comm._ctx, fast[2], fast[1], state.scale, side.cuda_stream)
+    reg = state._registered.get(bucket.index()) if state.zero_copy else None
+    if reg is None or reg[0] != buf.data_ptr() or reg[1] != buf.numel():
+        reg = state.registration_for(bucket.index(), buf) if state.zero_copy else None
+    if reg is None:
+        comm.allreduce_(buf, state.scale, stream=side)
+    else:
+        if reg[3] is not None:   # bucket lives in the multicast-bound region: in-switch, in place
+            rc = state._c_allreduce_nvls_inplace(comm._ctx, reg[3], reg[1], state.scale, side.cuda_stream)
+        else:                    # bucket mapped by the peers over IPC: one-pass reduce + push
+            rc = state._c_allreduce_registered(comm._ctx, reg[2], reg[1], state.scale, side.cuda_stream)
         if rc != 0:
             _lib.check(rc)
         _lib.launches += 2  # gate + data kernel
-    else:
-        reg = state.registration_for(bucket.index(), buf) if state.zero_copy else None
-        if reg is not None:
-            comm.allreduce_registered_(reg, buf, state.scale, stream=side)
-        else:
-            comm.allreduce_(buf, state.scale, stream=side)
     fut: torch.futures.Future[torch.Tensor] = torch.futures.Future(devices=[comm.device])
     torch.cuda.set_stream(side)
     try:
@@ -347,9 +393,54 @@ def p2p_allreduce_hook(state: HookState, bucket: dist.GradBucket) -> torch.futur
 
 def register_p2p_comm_hook(ddp_model, state: Optional[HookState] = None, **comm_kwargs) -> HookState:
     """``ddp_model.register_comm_hook(state, p2p_allreduce_hook)``; collective on first use."""
+    nvls_buckets = comm_kwargs.pop("nvls_buckets", None)
     state = state or HookState(**comm_kwargs)
     ddp_model.register_comm_hook(state, p2p_allreduce_hook)
+    if nvls_buckets is None:
+        nvls_buckets = os.environ.get("B2_AR_NVLS_BUCKETS", "1") != "0"
+    if nvls_buckets and state.zero_copy:
+        _place_buckets_in_nvls_region(ddp_model, state)
     return state
+
+
+_rebuild_pools: dict[int, "torch.cuda.MemPool"] = {}
+
+
+def _place_buckets_in_nvls_region(ddp_model, state: HookState) -> bool:
+    """Make the Reducer allocate its rebuilt buckets inside the communicator's multicast-bound
+    region, so that the NVSwitch can reduce them in place (no copy, no peer mapping).
+
+    The Reducer rebuilds its buckets exactly once, from ``DDP._pre_forward`` of the second
+    iteration (SP/torch/nn/parallel/distributed.py:1578-1584), through the Python-visible
+    ``reducer._rebuild_buckets()``. That one call is wrapped in ``torch.cuda.use_mem_pool`` with
+    a pool whose allocator is libb2ddp's b2_pool_alloc; every rank makes the same allocations in
+    the same order, so bucket i lands at the same offset everywhere (verified collectively by
+    ``registration_for`` before the in-place path is used). Collective; returns False on every
+    rank if NVLS is unavailable, leaving the IPC zero-copy path in charge."""
+    comm = state.comm
+    grad_bytes = sum(p.numel() * 4 for p in ddp_model.parameters() if p.requires_grad)
+    # segments are 2 MiB-aligned and torch rounds each bucket up to a 2 MiB multiple
+    need = int(grad_bytes * 1.15) + (64 << 20)
+    if not comm.enable_nvls(need + (64 << 20)):  # + the staging area in front of the pool
+        return False
+    pool = comm.nvls_pool()
+    if comm.nvls_pool_bytes < need:  # region was created earlier, too small: same answer on every rank
+        return False
+    _rebuild_pools[id(ddp_model.reducer)] = pool
+    Reducer = type(ddp_model.reducer)
+    if not getattr(Reducer, "_b200_rebuild_wrapped", False):
+        orig = Reducer._rebuild_buckets
+
+        def _rebuild_buckets(self):
+            p = _rebuild_pools.get(id(self))
+            if p is None:
+                return orig(self)
+            with torch.cuda.use_mem_pool(p):
+                return orig(self)
+
+        Reducer._rebuild_buckets = _rebuild_buckets
+        Reducer._b200_rebuild_wrapped = True
+    return True
 
 
 @torch.no_grad()

@@ -443,6 +443,11 @@ static int pick_algo(int world, long long bytes) {
 
 }  // namespace b2
 
+const void* b2_gate_kernel_for(int world) {
+  return world == 2 ? (const void*)b2::gate_kernel<2>
+       : world == 4 ? (const void*)b2::gate_kernel<4> : (const void*)b2::gate_kernel<8>;
+}
+
 extern "C" int b2_comm_create(int rank, int world, size_t staging_bytes, b2_comm** out) {
   using namespace b2;
   B2_REQUIRE(out, "comm_create: null out");

@@ -189,6 +189,7 @@ static inline int pick_blocks(long long npack, int max_blocks) {
 struct b2_nvls {  // NVLink multicast (in-switch reduction) state, see nvls.cu
   bool have_mc = false, ready = false;
   size_t bytes = 0;
+  size_t stage_bytes = 0;  // [0, stage_bytes) is the staging area of b2_allreduce_nvls; the pool starts after it
   CUmemGenericAllocationHandle mc = 0, mem = 0;
   CUdeviceptr uc_va = 0, mc_va = 0;
 };
@@ -219,4 +220,5 @@ struct b2_comm {
   unsigned long long timeout_ns = 30ull * 1000000000ull;
 };
 
-int b2_nvls_release(b2_comm* c);  // nvls.cu
+int b2_nvls_release(b2_comm* c);            // nvls.cu
+const void* b2_gate_kernel_for(int world);  // allreduce.cu: the one-CTA gate kernel for a world size

@@ -35,6 +35,11 @@
 
 namespace b2 {
 
+// communicator whose multicast-bound region backs the torch MemPool (one per process), and the
+// bump pointer inside it; used by b2_pool_alloc / b2_pool_free at the end of this file
+static b2_comm* g_pool_comm = nullptr;
+static size_t g_pool_next = 0;
+
 struct Drv {
   CUresult (*memGetAllocationGranularity)(size_t*, const CUmemAllocationProp*, CUmemAllocationGranularity_flags);
   CUresult (*memCreate)(CUmemGenericAllocationHandle*, size_t, const CUmemAllocationProp*, unsigned long long);
@@ -295,6 +300,12 @@ extern "C" int b2_nvls_bind(b2_comm* c) {
   B2_DRV_CHECK(d->memMap(n.mc_va, n.bytes, 0, n.mc, 0));
   B2_DRV_CHECK(d->memSetAccess(n.mc_va, n.bytes, &acc, 1));
   B2_CUDA_CHECK(cudaMemset((void*)n.uc_va, 0, n.bytes));
+  {
+    const size_t two_mib = 2ull << 20;
+    size_t st = n.bytes / 2 < (64ull << 20) ? n.bytes / 2 : (64ull << 20);
+    n.stage_bytes = st / two_mib * two_mib;
+    if (n.stage_bytes == 0) n.stage_bytes = n.bytes;  // tiny region: staging only, no pool
+  }
   n.ready = true;
   return B2_OK;
 }
@@ -306,7 +317,7 @@ extern "C" int b2_allreduce_nvls(b2_comm* c, void* buf, int64_t numel, float sca
   B2_REQUIRE(numel >= 0, "allreduce_nvls: negative numel");
   if (numel == 0) return B2_OK;
   B2_REQUIRE(buf && (((uintptr_t)buf) & 15) == 0, "allreduce_nvls: buffer null or not 16-byte aligned");
-  const long long cap = (long long)((c->nvls.bytes - 64) / 4 / 4 * 4);
+  const long long cap = (long long)((c->nvls.stage_bytes - 64) / 4 / 4 * 4);
   for (long long off = 0; off < numel; off += cap) {
     const long long n = (numel - off < cap) ? (numel - off) : cap;
     NvlsArgs a;
@@ -355,5 +366,151 @@ int b2_nvls_release(b2_comm* c) {
   }
   d->memRelease(n.mc);
   n = b2_nvls();
+  if (b2::g_pool_comm == c) {
+    b2::g_pool_comm = nullptr;
+    b2::g_pool_next = 0;
+  }
+  return B2_OK;
+}
+
+// ---- zero-copy NVLS: the buckets themselves live in the multicast-bound region ------------------
+//
+// The staging variant above pays a local copy in and out, which costs what the switch saves.
+// If the DDP buckets are ALLOCATED inside the multicast-bound region (a torch MemPool whose
+// allocator is b2_pool_alloc below, active only while the Reducer rebuilds its buckets), every
+// rank's bucket i sits at the same offset of its region, and the all-reduce is one pass over
+// the slice this rank owns: v = multimem.ld_reduce [mc + off + i]; multimem.st [mc + off + i],
+// v * scale - no copy, no peer reads, ~S bytes per NVLink direction in total.
+
+namespace b2 {
+
+template <int W>
+__global__ void __launch_bounds__(kArThreads, 1)
+allreduce_nvls_inplace_kernel(const __grid_constant__ NvlsArgs a, long long numel, float scale,
+                              uint32_t epoch, unsigned long long timeout_ns, int gated) {
+  const RankView& v = a.v;
+  const int rank = v.rank;
+  const int nb = gridDim.x, b = blockIdx.x, tid = threadIdx.x;
+  const long long npack = numel / 4;
+  const long long tail0 = npack * 4;
+  const long long Q = (npack + W - 1) / W;
+  const long long q = (Q + nb - 1) / nb;
+  constexpr int U = 4;
+  if (!gated) cross_barrier<W>(v, epoch, timeout_ns);
+  const long long slo = min((long long)rank * Q, npack), shi = min(slo + Q, npack);
+  const long long lo = min(slo + (long long)b * q, shi), hi = min(lo + q, shi);
+  long long i = lo + tid;
+  for (; i + (U - 1) * kArThreads < hi; i += U * kArThreads) {
+    uint4 t[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) t[u] = multimem_ld_reduce_f32x4(a.mc + (i + u * kArThreads) * 16);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      t[u].x = __float_as_uint(__fmul_rn(__uint_as_float(t[u].x), scale));
+      t[u].y = __float_as_uint(__fmul_rn(__uint_as_float(t[u].y), scale));
+      t[u].z = __float_as_uint(__fmul_rn(__uint_as_float(t[u].z), scale));
+      t[u].w = __float_as_uint(__fmul_rn(__uint_as_float(t[u].w), scale));
+      multimem_st_f32x4(a.mc + (i + u * kArThreads) * 16, t[u]);
+    }
+  }
+  for (; i < hi; i += kArThreads) {
+    uint4 t = multimem_ld_reduce_f32x4(a.mc + i * 16);
+    t.x = __float_as_uint(__fmul_rn(__uint_as_float(t.x), scale));
+    t.y = __float_as_uint(__fmul_rn(__uint_as_float(t.y), scale));
+    t.z = __float_as_uint(__fmul_rn(__uint_as_float(t.z), scale));
+    t.w = __float_as_uint(__fmul_rn(__uint_as_float(t.w), scale));
+    multimem_st_f32x4(a.mc + i * 16, t);
+  }
+  if (rank == 0 && b == 0 && tid < numel - tail0) {
+    char* p = a.mc + tail0 * 4 + (size_t)tid * 4;
+    multimem_st_f32(p, __fmul_rn(multimem_ld_reduce_f32(p), scale));
+  }
+  __threadfence_system();
+  cross_barrier<W>(v, epoch + 1, timeout_ns);
+}
+
+}  // namespace b2
+
+// torch.cuda.memory.CUDAPluggableAllocator entry points (alloc_fn / free_fn signatures): a bump
+// allocator over the multicast-bound region of the communicator attached with
+// b2_nvls_pool_attach. torch's caching allocator asks for whole segments and sub-allocates.
+extern "C" void* b2_pool_alloc(ssize_t size, int device, void* stream) {
+  (void)stream;
+  b2_comm* c = b2::g_pool_comm;
+  if (!c || !c->nvls.ready || device != c->device || size <= 0) return nullptr;
+  const size_t align = 2ull << 20;
+  if (b2::g_pool_next < c->nvls.stage_bytes) b2::g_pool_next = c->nvls.stage_bytes;
+  const size_t off = (b2::g_pool_next + align - 1) / align * align;
+  if (off + (size_t)size > c->nvls.bytes) return nullptr;  // torch reports out-of-memory
+  b2::g_pool_next = off + (size_t)size;
+  return (void*)(c->nvls.uc_va + off);
+}
+
+extern "C" void b2_pool_free(void* ptr, ssize_t size, int device, void* stream) {
+  (void)device; (void)stream;
+  b2_comm* c = b2::g_pool_comm;
+  if (!c || !ptr) return;
+  const size_t off = (size_t)((CUdeviceptr)(uintptr_t)ptr - c->nvls.uc_va);
+  if (off + (size_t)size == b2::g_pool_next) b2::g_pool_next = off;  // last block: reuse; others stay reserved
+}
+
+extern "C" int b2_nvls_pool_attach(b2_comm* c) {
+  using namespace b2;
+  B2_REQUIRE(c, "nvls_pool_attach: null comm");
+  if (!c->nvls.ready) return fail(B2_ERR_STATE, "nvls_pool_attach: b2_nvls_bind has not completed");
+  if (g_pool_comm && g_pool_comm != c) return fail(B2_ERR_STATE, "nvls_pool_attach: another communicator already backs the pool");
+  g_pool_comm = c;
+  return B2_OK;
+}
+
+extern "C" int b2_nvls_region(b2_comm* c, uint64_t* base_out, uint64_t* bytes_out, uint64_t* pool_offset_out) {
+  using namespace b2;
+  B2_REQUIRE(c && base_out && bytes_out && pool_offset_out, "nvls_region: null pointer");
+  if (!c->nvls.ready) return fail(B2_ERR_STATE, "nvls_region: b2_nvls_bind has not completed");
+  *base_out = (uint64_t)c->nvls.uc_va;
+  *bytes_out = (uint64_t)c->nvls.bytes;
+  *pool_offset_out = (uint64_t)c->nvls.stage_bytes;  // the pool hands out [pool_offset, bytes)
+  return B2_OK;
+}
+
+extern "C" int b2_allreduce_nvls_inplace(b2_comm* c, uint64_t offset_bytes, int64_t numel, float scale,
+                                         b2_stream_t stream) {
+  using namespace b2;
+  B2_REQUIRE(c, "allreduce_nvls_inplace: null comm");
+  if (!c->nvls.ready) return fail(B2_ERR_STATE, "allreduce_nvls_inplace: b2_nvls_bind has not completed");
+  B2_REQUIRE(numel >= 0 && (offset_bytes & 15) == 0 && offset_bytes + (uint64_t)numel * 4 <= c->nvls.bytes,
+             "allreduce_nvls_inplace: [%llu, +%lld floats) is outside the %zu-byte region or misaligned",
+             (unsigned long long)offset_bytes, (long long)numel, c->nvls.bytes);
+  if (numel == 0) return B2_OK;
+  NvlsArgs a;
+  a.v.buf = (float*)(c->nvls.uc_va + offset_bytes);
+  a.v.rank = c->rank;
+  for (int r = 0; r < B2_MAX_WORLD; ++r) {
+    const int k = r < c->world ? r : c->rank;
+    a.v.stage[r] = nullptr;
+    a.v.flags[r] = (uint32_t*)c->base[k];
+  }
+  a.v.status = (uint32_t*)(c->base[c->rank] + kStatusOff);
+  a.uc = (char*)(c->nvls.uc_va + offset_bytes);
+  a.mc = (char*)(c->nvls.mc_va + offset_bytes);
+  uint32_t epoch = c->epoch;
+  unsigned long long to = c->timeout_ns;
+  int gated = 1;
+  {
+    ArArgs<1> g;
+    g.v[0] = a.v;
+    const void* gate = b2_gate_kernel_for(c->world);
+    void* gargs[] = {&g, &epoch, &to};
+    B2_CUDA_CHECK(cudaLaunchKernel(gate, dim3(1), dim3(32), gargs, 0, (cudaStream_t)stream));
+  }
+  const void* fn = c->world == 2 ? (const void*)allreduce_nvls_inplace_kernel<2>
+                 : c->world == 4 ? (const void*)allreduce_nvls_inplace_kernel<4>
+                                 : (const void*)allreduce_nvls_inplace_kernel<8>;
+  const int nb = pick_blocks(numel / 4 / c->world, c->max_blocks);
+  long long n_arg = numel;
+  float scale_arg = scale;
+  void* kargs[] = {&a, &n_arg, &scale_arg, &epoch, &to, &gated};
+  B2_CUDA_CHECK(cudaLaunchKernel(fn, dim3(nb), dim3(kArThreads), kargs, 0, (cudaStream_t)stream));
+  c->epoch += 2;
   return B2_OK;
 }

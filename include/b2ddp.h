@@ -22,6 +22,7 @@
 
 #include <stddef.h>
 #include <stdint.h>
+#include <sys/types.h> /* ssize_t */
 
 #ifdef __cplusplus
 extern "C" {
@@ -233,6 +234,21 @@ int b2_nvls_import(b2_comm* c, int fd, size_t rounded_bytes);
 int b2_nvls_add_device(b2_comm* c);
 int b2_nvls_bind(b2_comm* c);
 int b2_allreduce_nvls(b2_comm* c, void* buf, int64_t numel, float scale, b2_stream_t stream);
+/* Zero-copy NVLS: buffers ALLOCATED inside the multicast-bound region (same offset on every
+ * rank) are reduced in place by the switch with no copy at all: a one-CTA gate kernel, then one
+ * pass  v = multimem.ld_reduce [mc+off+i]; multimem.st [mc+off+i], v*scale  over the slice this
+ * rank owns, then one barrier. b2_nvls_region reports the region (unicast base address, bytes,
+ * and the offset where the pool starts: the bytes before it are b2_allreduce_nvls's staging);
+ * b2_nvls_pool_attach makes it the backing store of b2_pool_alloc / b2_pool_free, which have the
+ * alloc_fn / free_fn signatures of torch.cuda.memory.CUDAPluggableAllocator (a bump allocator
+ * handing torch's caching allocator whole segments), so that a torch MemPool active while the
+ * DDP Reducer rebuilds its buckets places the buckets in the region. */
+int b2_nvls_region(b2_comm* c, uint64_t* base_out, uint64_t* bytes_out, uint64_t* pool_offset_out);
+int b2_nvls_pool_attach(b2_comm* c);
+void* b2_pool_alloc(ssize_t size, int device, void* stream);
+void b2_pool_free(void* ptr, ssize_t size, int device, void* stream);
+int b2_allreduce_nvls_inplace(b2_comm* c, uint64_t offset_bytes, int64_t numel, float scale,
+                              b2_stream_t stream);
 /* 0, or B2_ERR_TIMEOUT once a kernel gave up waiting for a peer (sticky). */
 int b2_comm_status(b2_comm* c);
 int b2_comm_destroy(b2_comm* c);

@@ -141,10 +141,10 @@ def _worker(rank, world, port, q):
                 results[(n, "registered", rep)] = bool(np.array_equal(x.cpu().numpy(), O.allreduce_mean(bufs)))
             comm.unregister(reg)
         # in-switch reduction (NVLS): identical on every rank, fp32-rounding-equal to the oracle
-        nvls_ok = comm.enable_nvls(8 << 20)
+        nvls_ok = comm.enable_nvls(512 << 20)
         results[("nvls_enabled", comm.nvls_error)] = bool(nvls_ok)
         if nvls_ok:
-            for n in (3, 4100, 1 << 20, (8 << 20) // 4 * 2 + 9):  # the last one is chunked
+            for n in (3, 4100, 1 << 20, (64 << 20) // 4 * 2 + 9):  # the last one is chunked over the staging area
                 bufs = allreduce_inputs(world, n, 700 + n % 89)
                 x = torch.from_numpy(bufs[rank].copy()).cuda()
                 comm.allreduce_nvls_(x, 1.0 / world)
@@ -154,6 +154,25 @@ def _worker(rank, world, port, q):
                 parts = [torch.empty_like(x) for _ in range(world)]
                 dist.all_gather(parts, x)
                 results[(n, "nvls")] = close and all(torch.equal(parts[0], t) for t in parts)
+            # zero-copy NVLS: a tensor allocated inside the multicast-bound region, reduced in place
+            pool = comm.nvls_pool()
+            for n in (7, 4100, (3 << 20) + 5):
+                with torch.cuda.use_mem_pool(pool):
+                    x = torch.empty(n, device="cuda")
+                off = comm.nvls_offset(x)
+                offs = [None] * world
+                dist.all_gather_object(offs, off)
+                for rep in range(2):
+                    bufs = allreduce_inputs(world, n, 800 + rep + n % 89)
+                    x.copy_(torch.from_numpy(bufs[rank]))
+                    comm.allreduce_nvls_inplace_(off, n, 1.0 / world)
+                    torch.cuda.synchronize()
+                    parts = [torch.empty_like(x) for _ in range(world)]
+                    dist.all_gather(parts, x)
+                    ok = (off is not None and len(set(offs)) == 1 and
+                          np.allclose(x.cpu().numpy(), O.allreduce_mean(bufs), rtol=1e-6, atol=1e-9) and
+                          all(torch.equal(parts[0], t) for t in parts))
+                    results[(n, "nvls_inplace", rep)] = bool(ok)
 
         # train-task.py's average_gradients(model): one flat exchange, bit-exact vs the oracle, and
         # the second call reuses the registered flat buffer
@@ -193,6 +212,8 @@ def _worker(rank, world, port, q):
                 opt.step(); opt.zero_grad()
             if use_hook:
                 assert hook_state._registered, "no bucket was registered for zero-copy"
+                kinds = {("nvls" if r[3] is not None else "ipc") for r in hook_state._registered.values()}
+                results[("hook_bucket_paths", tuple(sorted(kinds)))] = True
             return [p.detach().clone() for p in model.parameters()]
 
         a, b = run(True), run(False)

@@ -290,7 +290,7 @@ def _vote_worker(rank, world, port, q):
         r1 = st.registration_for(3, _Buf(0x1000 + rank, big))
         r2 = st.registration_for(3, _Buf(0x1000 + rank, big))  # cached, no collective
         peers = st.comm.registered[0]
-        ok_basic = (r0 is None and r1 == 0 and r2 == 0 and
+        ok_basic = (r0 is None and r1 == (0x1000 + rank, big, 0, None) and r2 == r1 and
                     peers == [(bytes([r]) * 64, 512 * r) for r in range(world)])
         # a bucket below the size threshold never votes
         ok_small = st.registration_for(0, _Buf(0x2000, 16)) is None and 0 not in st._last_seen
@@ -299,7 +299,7 @@ def _vote_worker(rank, world, port, q):
         st2.registration_for(5, _Buf(0x3000, big))
         moved = st2.registration_for(5, _Buf(0x3000 + (0x100 if rank == 1 else 0), big))
         again = st2.registration_for(5, _Buf(0x3000 + (0x100 if rank == 1 else 0), big))
-        ok_move = moved is None and again == 0
+        ok_move = moved is None and again is not None and again[2] == 0
         # memory that cannot be exported on one rank (expandable segments) -> nobody registers
         st3 = state(exportable=(rank != 0))
         st3.registration_for(7, _Buf(0x4000, big))
