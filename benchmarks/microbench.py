@@ -269,7 +269,8 @@ def bench_allreduce(args):
         if world > 1 and nvls:
             rows.append(("b200_fp32_nvls_staged", timed(lambda: comm.allreduce_nvls_(x, 1.0 / world), iters, args.warmup)))
             with torch.cuda.use_mem_pool(pool):
-                xp = torch.randn(n, device="cuda") * 1e-2
+                xp = torch.empty(n, device="cuda")  # exactly one allocation inside the region
+            xp.normal_().mul_(1e-2)
             off = comm.nvls_offset(xp)
             if off is not None:
                 rows.append(("b200_fp32_nvls_zero_copy",
