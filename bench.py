@@ -150,10 +150,27 @@ def grad_sync_probe(harness, impl: str, world: int, bucket_mb: float = 25.0, ite
     dev = harness.device
     n = int(bucket_mb * (1 << 20)) // 4
     x = torch.randn(n, device=dev) * 1e-2
+    path = "nccl div_ + all_reduce"
     if impl == "b200":
         comm = harness.hook_state.comm if harness.hook_state is not None else harness.comm
-        reg = comm.register(x)
-        fn = lambda: comm.allreduce_registered_(reg, x, 1.0 / world)  # noqa: E731
+        off = None
+        if comm.nvls and comm._pool is not None:
+            # the Reducer's buckets live in the multicast-bound region: probe the same path
+            with torch.cuda.use_mem_pool(comm._pool):
+                xp = torch.empty(n, device=dev)
+            off = comm.nvls_offset(xp)
+            offs = [None] * world
+            dist.all_gather_object(offs, off)
+            if off is None or len(set(offs)) != 1:
+                off = None
+        if off is not None:
+            xp.copy_(x)
+            fn = lambda: comm.allreduce_nvls_inplace_(off, n, 1.0 / world)  # noqa: E731
+            path = "zero-copy NVLS: in-switch reduction in place on buckets in multicast-bound memory"
+        else:
+            reg = comm.register(x)
+            fn = lambda: comm.allreduce_registered_(reg, x, 1.0 / world)  # noqa: E731
+            path = "zero-copy one-pass push over peer-mapped (IPC) buckets"
     else:
         def fn():
             x.div_(world)
@@ -175,7 +192,7 @@ def grad_sync_probe(harness, impl: str, world: int, bucket_mb: float = 25.0, ite
     bus = n * 4 * 2 * (world - 1) / world / ms / 1e6
     return {"bucket_mb": bucket_mb, "us_per_bucket": ms * 1e3, "bus_gbs": bus, "nvlink_peak_gbs": 900.0,
             "frac_of_nvlink_peak": bus / 900.0, "frac_of_measured_peer_copy_770": bus / 770.0,
-            "impl": "zero-copy one-pass push over peer-mapped buckets" if impl == "b200" else "nccl div_ + all_reduce"}
+            "impl": path}
 
 
 def run_cpu(args, steps: int, warmup: int):
@@ -300,6 +317,13 @@ def main():
            "params": n_params, "lib": str(_lib.lib_path().name) if args.impl == "b200" else None}
     if world > 1:
         out["grad_sync"] = grad_sync_probe(h, args.impl, world)
+        if h.hook_state is not None:  # which path the Reducer's buckets actually took
+            regs = h.hook_state._registered.values()
+            out["grad_sync"]["ddp_buckets"] = {
+                "reduced_per_step": h.hook_state.buckets_reduced // max(1, h.steps_done),
+                "nvls_in_place": sum(1 for r in regs if r[3] is not None),
+                "ipc_push_in_place": sum(1 for r in regs if r[3] is None),
+            }
     h.close()
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline and args.impl == "b200":
