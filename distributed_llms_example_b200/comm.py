@@ -397,7 +397,11 @@ def register_p2p_comm_hook(ddp_model, state: Optional[HookState] = None, **comm_
     state = state or HookState(**comm_kwargs)
     ddp_model.register_comm_hook(state, p2p_allreduce_hook)
     if nvls_buckets is None:
-        nvls_buckets = os.environ.get("B2_AR_NVLS_BUCKETS", "1") != "0"
+        # measured (profiles/README.md): the switch wins at world 8 (25 MiB bucket 90.7 us vs 100.7 us
+        # for the IPC push, 146.6 us for NCCL); at world 2 it has no byte advantage and loses
+        # (97 us vs 64 us), world 4 is unmeasured and stays on the IPC push
+        env = os.environ.get("B2_AR_NVLS_BUCKETS", "auto")
+        nvls_buckets = state.comm.world >= 8 if env == "auto" else env != "0"
     if nvls_buckets and state.zero_copy:
         _place_buckets_in_nvls_region(ddp_model, state)
     return state
