@@ -424,7 +424,7 @@ def _place_buckets_in_nvls_region(ddp_model, state: HookState) -> bool:
     comm = state.comm
     grad_bytes = sum(p.numel() * 4 for p in ddp_model.parameters() if p.requires_grad)
     # segments are 2 MiB-aligned and torch rounds each bucket up to a 2 MiB multiple
-    need = int(grad_bytes * 1.15) + (64 << 20)
+    need = int(grad_bytes * 1.25) + (128 << 20)
     if not comm.enable_nvls(need + (64 << 20)):  # + the staging area in front of the pool
         return False
     pool = comm.nvls_pool()

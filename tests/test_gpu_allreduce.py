@@ -196,14 +196,15 @@ def _worker(rank, world, port, q):
         comm.check()
 
         # DDP comm hook vs stock DDP on the same model / data: 3 steps, identical parameters
-        def run(use_hook):
+        def run(use_hook, nvls_buckets=False):
             torch.manual_seed(0)
             model = torch.nn.Sequential(torch.nn.Linear(512, 2048), torch.nn.ReLU(), torch.nn.Linear(2048, 4096),
                                         torch.nn.ReLU(), torch.nn.Linear(4096, 512)).cuda()
             ddp = torch.nn.parallel.DistributedDataParallel(model, device_ids=[rank], bucket_cap_mb=4)
             hook_state = None
             if use_hook:
-                hook_state = register_p2p_comm_hook(ddp, comm=comm, zero_copy_min_bytes=1 << 20)
+                hook_state = register_p2p_comm_hook(ddp, comm=comm, zero_copy_min_bytes=1 << 20,
+                                                    nvls_buckets=nvls_buckets)
             opt = torch.optim.SGD(ddp.parameters(), lr=0.1)
             g = torch.Generator(device="cuda").manual_seed(1234 + rank)
             for _ in range(5):  # long enough for the buckets to be registered (zero-copy) on step 3
@@ -217,6 +218,12 @@ def _worker(rank, world, port, q):
             return [p.detach().clone() for p in model.parameters()]
 
         a, b = run(True), run(False)
+        if nvls_ok:
+            # same model with the Reducer's buckets placed in the multicast-bound region
+            c = run(True, nvls_buckets=True)
+            results[("hook_nvls_buckets_used", True)] = ("hook_bucket_paths", ("nvls",)) in results
+            excess = max(float(((x - y).abs() - 1e-5 * y.abs()).max()) for x, y in zip(c, b))
+            results[("hook_nvls_buckets_match_stock", excess)] = excess < 1e-7
         # NCCL's ring/tree order differs from rank order, so after 5 SGD steps the two runs agree
         # to fp32 rounding, not bit for bit: |x - y| <= 1e-5 |y| + 1e-7 (worst excess reported)
         worst = max(float(((x - y).abs() - 1e-5 * y.abs()).max()) for x, y in zip(a, b))
