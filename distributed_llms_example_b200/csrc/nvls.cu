@@ -352,6 +352,11 @@ int b2_nvls_release(b2_comm* c) {
   using namespace b2;
   b2_nvls& n = c->nvls;
   if (!n.have_mc) return B2_OK;
+  if (g_pool_comm == c && g_pool_next > n.stage_bytes) {
+    // torch's caching allocator still owns segments inside the region (DDP buckets): unmapping
+    // would leave it with dangling blocks. Keep the mappings; process teardown reclaims them.
+    return B2_OK;
+  }
   Drv* d;
   if (drv(&d) != B2_OK) return B2_OK;
   if (n.ready) {
@@ -366,9 +371,9 @@ int b2_nvls_release(b2_comm* c) {
   }
   d->memRelease(n.mc);
   n = b2_nvls();
-  if (b2::g_pool_comm == c) {
-    b2::g_pool_comm = nullptr;
-    b2::g_pool_next = 0;
+  if (g_pool_comm == c) {
+    g_pool_comm = nullptr;
+    g_pool_next = 0;
   }
   return B2_OK;
 }
