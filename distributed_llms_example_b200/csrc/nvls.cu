@@ -355,6 +355,8 @@ int b2_nvls_release(b2_comm* c) {
   if (g_pool_comm == c && g_pool_next > n.stage_bytes) {
     // torch's caching allocator still owns segments inside the region (DDP buckets): unmapping
     // would leave it with dangling blocks. Keep the mappings; process teardown reclaims them.
+    // The communicator object itself is about to be deleted: detach it from the pool entry points.
+    g_pool_comm = nullptr;
     return B2_OK;
   }
   Drv* d;
