@@ -56,6 +56,7 @@ def parse_args():
     ap.add_argument("--grad-accum", type=int, default=1)
     ap.add_argument("--label-mode", default="REF", choices=["REF", "MASK"])
     ap.add_argument("--wire", default="fp32", choices=["fp32", "bf16"])
+    ap.add_argument("--bucket-cap-mb", type=float, default=None, help="DDP bucket size (default: torch's 25 MiB)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-steps", type=int, default=2, help="timed CPU steps for cpu_baseline")
     return ap.parse_args()
@@ -257,7 +258,8 @@ def main():
 
     cfg = StepConfig(model=args.model, semantics=args.semantics, impl=args.impl, device=f"cuda:{local_rank}",
                      batch_size=args.batch_size, grad_accum=args.grad_accum, label_mode=args.label_mode,
-                     bf16=True, wire=args.wire, total_steps=max(1000, 4 * (args.steps + args.warmup)))
+                     bf16=True, wire=args.wire, bucket_cap_mb=args.bucket_cap_mb,
+                     total_steps=max(1000, 4 * (args.steps + args.warmup)))
     h = StepHarness(cfg)
     n_params = sum(p.numel() for p in h.model.parameters())
     ga, K, W = args.grad_accum, args.steps, max(args.warmup, 0)

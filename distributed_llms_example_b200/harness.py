@@ -53,6 +53,7 @@ class StepConfig:
     max_grad_norm: float = 1.0          # trainer semantics only
     fused_adamw: Optional[bool] = None  # stock impl: torch's fused kernel (what Trainer selects)
     wire: str = "fp32"                  # b200 impl: dtype on NVLink
+    bucket_cap_mb: Optional[float] = None  # DDP bucket size; None = torch's default (25 MiB)
 
 
 def _no_decay(name: str) -> bool:
@@ -119,7 +120,8 @@ class StepHarness:
                 from torch.nn.parallel import DistributedDataParallel as DDP
 
                 ids = [self.device.index] if self.device.type == "cuda" else None
-                self.ddp = DDP(self.model, device_ids=ids, find_unused_parameters=False)
+                extra = {} if cfg.bucket_cap_mb is None else {"bucket_cap_mb": cfg.bucket_cap_mb}
+                self.ddp = DDP(self.model, device_ids=ids, find_unused_parameters=False, **extra)
                 if cfg.impl == "b200":
                     from .comm import register_p2p_comm_hook
 
