@@ -261,6 +261,12 @@ class AdamW(Optimizer):
         self.grad_scale = out[1:2]
         return out[0]
 
+    def zero_grad(self, set_to_none: bool = True) -> None:
+        """As torch, and drops a clip coefficient that was computed for these gradients but never
+        consumed by a step (so it cannot leak into the next iteration)."""
+        self.grad_scale = None
+        super().zero_grad(set_to_none=set_to_none)
+
     # -- step ----------------------------------------------------------------------
     @torch.no_grad()
     def step(self, closure: Optional[Callable[[], float]] = None):
