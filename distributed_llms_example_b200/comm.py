@@ -303,7 +303,7 @@ class HookState:
         if zero_copy is None:
             zero_copy = os.environ.get("B2_AR_ZERO_COPY", "1") != "0"
         if zero_copy_min_bytes is None:
-            # measured crossover against the one-barrier staging path (profiles/allreduce_*.md)
+            # measured crossover against the one-barrier staging path (profiles/README.md)
             dflt = {2: 16 << 20, 4: 8 << 20}.get(self.comm.world, 2 << 20)
             zero_copy_min_bytes = int(os.environ.get("B2_AR_ZERO_COPY_MIN_BYTES", str(dflt)))
         self.zero_copy = bool(zero_copy) and self.comm.world > 1 and self.comm.wire == "fp32"
