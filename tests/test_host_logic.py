@@ -401,3 +401,32 @@ def test_config1_reference_cpu_path_world_2_gloo():
         assert err is None, f"rank {rank}:\n{err}"
         assert wrapped and same and len(losses) == 3 and all(np.isfinite(losses))
     assert outs[0][1] != outs[1][1]  # different shards of synthetic data per rank
+
+
+def test_trainer_semantics_decay_groups_match_hf_trainer():
+    """The harness's Trainer semantics put weight_decay=0.01 on exactly the parameters HF Trainer
+    decays (Trainer.get_decay_parameter_names; tied aliases of shared.weight aside)."""
+    from transformers import Trainer
+
+    from distributed_llms_example_b200.harness import _no_decay
+    from distributed_llms_example_b200.synthetic import build_model
+
+    m = build_model("t5-small")
+    hf = set(Trainer.get_decay_parameter_names(Trainer.__new__(Trainer), m))
+    own = {n for n, _ in m.named_parameters()}
+    assert {n for n in own if not _no_decay(n)} == hf & own
+    assert all("layer_norm" in n for n in own - hf)  # T5 has no biases: only the norms are exempt
+
+
+def test_synthetic_features_are_deterministic_per_rank_and_shaped_like_the_scripts():
+    from distributed_llms_example_b200.synthetic import make_features
+
+    a, b, c = make_features(3, rank=0), make_features(3, rank=0), make_features(3, rank=1)
+    assert a == b and a != c  # seed 1234 + rank
+    for f in a:
+        assert len(f["input_ids"]) == 512 == len(f["attention_mask"]) and len(f["labels"]) == 128
+        n = sum(f["attention_mask"])
+        assert f["input_ids"][n - 1] == 1 and all(t == 0 for t in f["input_ids"][n:])  # eos, then pad 0
+        assert -100 not in f["labels"]  # REF mode: what the scripts really feed (SURVEY F6)
+    m = make_features(3, rank=0, label_mode="MASK")
+    assert all(8 < len(f["labels"]) <= 128 and f["labels"][-1] == 1 for f in m)  # ragged, eos-terminated
