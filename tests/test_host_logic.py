@@ -415,7 +415,8 @@ def test_trainer_semantics_decay_groups_match_hf_trainer():
     hf = set(Trainer.get_decay_parameter_names(Trainer.__new__(Trainer), m))
     own = {n for n, _ in m.named_parameters()}
     assert {n for n in own if not _no_decay(n)} == hf & own
-    assert all("layer_norm" in n for n in own - hf)  # T5 has no biases: only the norms are exempt
+    # exempt: the T5LayerNorm weights and the relative_attention_bias tables (name contains "bias")
+    assert all("layer_norm" in n or "bias" in n for n in own - hf)
 
 
 def test_synthetic_features_are_deterministic_per_rank_and_shaped_like_the_scripts():
