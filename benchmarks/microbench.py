@@ -222,6 +222,32 @@ def bench_ce_kernel(args):
 
 
 # ------------------------------------------------------------------------------------------
+def bench_allreduce_emulated(args):
+    """One GPU, W virtual ranks in ONE cooperative launch (b2_allreduce_emulated): the same device
+    code as the multi-GPU kernels, runnable under ncu (which must never wrap a multi-rank command).
+    Buffers are local, so timings say nothing about NVLink; the capture shows instruction mix,
+    stalls and local traffic of the staging (1, 2), in-place pull (3) and push (4) kernels."""
+    import ctypes
+
+    from distributed_llms_example_b200 import _lib as L
+
+    lib = L.load()
+    w = 8
+    for mb in args.sizes_mb:
+        n = int(mb * (1 << 20)) // 4
+        bufs = [torch.randn(n, device="cuda") * 1e-2 for _ in range(w)]
+        scratch = torch.empty(lib.b2_allreduce_emulated_scratch_bytes(w, n), dtype=torch.uint8, device="cuda")
+        ptrs = (ctypes.c_void_p * w)(*[b.data_ptr() for b in bufs])
+        for algo in (2, 4):
+            def fn():
+                L.check(lib.b2_allreduce_emulated(ptrs, w, n, 0, 1.0 / w, algo, scratch.data_ptr(),
+                                                  torch.cuda.current_stream().cuda_stream))
+            med, _ = time_ms(fn, max(3, args.iters), 2, False)
+            emit(bench="allreduce_emulated", world=w, size_mb=mb, algo={2: "two_shot_staging", 4: "push_in_place"}[algo],
+                 ms=med, note="single GPU, local buffers: not an NVLink number")
+
+
+# ------------------------------------------------------------------------------------------
 def bench_allreduce(args):
     from distributed_llms_example_b200.comm import P2PComm
 
@@ -301,7 +327,7 @@ def bench_allreduce(args):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("bench", choices=["adamw", "ce", "ce_kernel", "allreduce"])
+    ap.add_argument("bench", choices=["adamw", "ce", "ce_kernel", "allreduce", "allreduce_emulated"])
     ap.add_argument("--models", nargs="+", default=["t5-small", "flan-t5-base", "flan-t5-large", "flan-t5-xl"])
     ap.add_argument("--rows", nargs="+", type=int, default=[128, 1024, 8192, 32768])
     ap.add_argument("--sizes-mb", nargs="+", type=float, default=[1, 2, 4, 8, 16, 25, 32, 64, 128, 256, 512, 1024])
@@ -312,7 +338,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--only", default="all", choices=["all", "ours"])
     args = ap.parse_args()
-    {"adamw": bench_adamw, "ce": bench_ce, "ce_kernel": bench_ce_kernel, "allreduce": bench_allreduce}[args.bench](args)
+    {"adamw": bench_adamw, "ce": bench_ce, "ce_kernel": bench_ce_kernel, "allreduce": bench_allreduce,
+     "allreduce_emulated": bench_allreduce_emulated}[args.bench](args)
 
 
 if __name__ == "__main__":
