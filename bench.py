@@ -275,6 +275,7 @@ def main():
     if args.impl == "b200":
         h.optimizer.kernel_events = []
     launches0 = _lib.launches
+    cpp_fast0 = h.hook_state.cpp_handle.fast_calls if (h.hook_state is not None and h.hook_state.cpp_handle is not None) else 0
     with ClockSampler(local_rank) as clocks:
         # cudaProfilerStart/Stop bracket the timed region so that `ncu --profile-from-start off`
         # lists exactly these K steps' launches (no-ops when no profiler is attached)
@@ -282,6 +283,8 @@ def main():
         ms_res, _ = timed_region(h, resident, read_loss=False)
         torch.cuda.profiler.stop()
         launches = _lib.launches - launches0
+        if h.hook_state is not None and h.hook_state.cpp_handle is not None:
+            launches += 2 * (h.hook_state.cpp_handle.fast_calls - cpp_fast0)  # gate + data kernel each
         opt_events = h.optimizer.kernel_events if args.impl == "b200" else None
         if args.impl == "b200":
             h.optimizer.kernel_events = None
@@ -322,7 +325,8 @@ def main():
         if h.hook_state is not None:  # which path the Reducer's buckets actually took
             regs = h.hook_state._registered.values()
             out["grad_sync"]["ddp_buckets"] = {
-                "reduced_per_step": h.hook_state.buckets_reduced // max(1, h.steps_done),
+                "reduced_per_step": h.hook_state.total_buckets_reduced // max(1, h.steps_done),
+                "cpp_hook": h.hook_state.cpp_handle is not None,
                 "nvls_in_place": sum(1 for r in regs if r[3] is not None),
                 "ipc_push_in_place": sum(1 for r in regs if r[3] is None),
             }

@@ -84,6 +84,35 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     return LIB_PATH
 
 
+HOOK_SRC = PKG_DIR / "csrc_torch" / "ddp_hook.cpp"
+HOOK_LIB = PKG_DIR / "_b2ddp_hook.so"
+
+
+def build_hook(force: bool = False, verbose: bool = False) -> Path:
+    """Compile the C++ DDP comm hook (the only source that includes torch headers) in-tree with
+    torch.utils.cpp_extension; no-op when the source is unchanged."""
+    stamp = PKG_DIR / ".b2ddp_hook.stamp"
+    fp = hashlib.sha256(HOOK_SRC.read_bytes()).hexdigest()
+    try:
+        import torch
+
+        fp += torch.__version__
+    except Exception as exc:  # pragma: no cover
+        raise RuntimeError(f"torch is required to build the DDP hook: {exc}")
+    if not force and HOOK_LIB.exists() and stamp.exists() and stamp.read_text() == fp:
+        return HOOK_LIB
+    import torch.utils.cpp_extension as ce
+
+    bdir = PKG_DIR / "build" / "hook"
+    bdir.mkdir(parents=True, exist_ok=True)
+    ce.load(name="_b2ddp_hook", sources=[str(HOOK_SRC)], extra_cflags=["-O2", "-std=c++17"], with_cuda=True,
+            build_directory=str(bdir), verbose=verbose, is_python_module=False)
+    shutil.copy2(bdir / "_b2ddp_hook.so", HOOK_LIB)
+    stamp.write_text(fp)
+    return HOOK_LIB
+
+
 if __name__ == "__main__":
     path = build(force="--force" in sys.argv, verbose="--verbose" in sys.argv)
     print(path)
+    print(build_hook(force="--force" in sys.argv, verbose="--verbose" in sys.argv))

@@ -311,6 +311,11 @@ class HookState:
         self._last_seen: dict[int, tuple] = {}    # bucket index -> (data_ptr, numel) at its last call
         self._registered: dict[int, tuple] = {}   # bucket index -> (data_ptr, numel, reg_id | None, nvls offset | None)
         self._c_allreduce_nvls_inplace = self.comm._lib.b2_allreduce_nvls_inplace
+        self.cpp_handle = None  # set when the C++ hook serves the registered buckets
+
+    @property
+    def total_buckets_reduced(self) -> int:
+        return self.buckets_reduced + (self.cpp_handle.fast_calls if self.cpp_handle is not None else 0)
 
     def registration_for(self, index: int, buf: torch.Tensor) -> Optional[tuple]:
         """Collective while the bucket is unregistered: every rank contributes (stable?, handle,
@@ -347,6 +352,9 @@ class HookState:
         else:
             return None  # mixed placement across ranks: stay on the staging path
         self._registered[index] = reg
+        if self.cpp_handle is not None:  # from now on the C++ hook handles this bucket by itself
+            self.cpp_handle.set_entry(index, reg[0], reg[1], 1 if reg[3] is not None else 0,
+                                      reg[3] if reg[3] is not None else reg[2])
         return reg
 
 
@@ -391,11 +399,52 @@ def p2p_allreduce_hook(state: HookState, bucket: dist.GradBucket) -> torch.futur
     return fut
 
 
+_cpp_hook_module = None
+
+
+def _load_cpp_hook():
+    """The in-tree C++ hook extension (csrc_torch/ddp_hook.cpp), or None if it has not been built."""
+    global _cpp_hook_module
+    if _cpp_hook_module is None:
+        import importlib.util
+
+        from .build import HOOK_LIB
+
+        if not HOOK_LIB.exists():
+            return None
+        spec = importlib.util.spec_from_file_location("_b2ddp_hook", str(HOOK_LIB))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        _cpp_hook_module = mod
+    return _cpp_hook_module
+
+
 def register_p2p_comm_hook(ddp_model, state: Optional[HookState] = None, **comm_kwargs) -> HookState:
-    """``ddp_model.register_comm_hook(state, p2p_allreduce_hook)``; collective on first use."""
+    """Attach the peer-memory all-reduce to a DDP module; collective on first use.
+
+    With ``cpp_hook=True`` (or ``B2_CPP_HOOK=1``) the Reducer gets the C++ hook of
+    csrc_torch/ddp_hook.cpp, which serves registered buckets without touching the interpreter and
+    delegates everything else to ``p2p_allreduce_hook``; otherwise the Python hook is registered
+    through ``ddp_model.register_comm_hook``."""
     nvls_buckets = comm_kwargs.pop("nvls_buckets", None)
+    cpp_hook = comm_kwargs.pop("cpp_hook", None)
     state = state or HookState(**comm_kwargs)
-    ddp_model.register_comm_hook(state, p2p_allreduce_hook)
+    if cpp_hook is None:
+        cpp_hook = os.environ.get("B2_CPP_HOOK", "0") == "1"
+    mod = _load_cpp_hook() if cpp_hook else None
+    if cpp_hook and mod is None:
+        raise RuntimeError("B2_CPP_HOOK=1 but _b2ddp_hook.so is not built "
+                           "(python -m distributed_llms_example_b200.build)")
+    if mod is not None:
+        lib = state.comm._lib
+        fn_reg = C.cast(lib.b2_allreduce_registered, C.c_void_p).value
+        fn_nvls = C.cast(lib.b2_allreduce_nvls_inplace, C.c_void_p).value
+        side = state.stream
+        state.cpp_handle = mod.attach(ddp_model.reducer, p2p_allreduce_hook, state, state.comm._ctx.value, fn_reg,
+                                      fn_nvls, state.scale, state.comm.device.index, side.stream_id)
+        ddp_model._comm_hooks.append((p2p_allreduce_hook, state))  # what DDP.register_comm_hook records
+    else:
+        ddp_model.register_comm_hook(state, p2p_allreduce_hook)
     if nvls_buckets is None:
         # measured (profiles/README.md): the switch wins at world 8 (25 MiB bucket 90.7 us vs 100.7 us
         # for the IPC push, 146.6 us for NCCL); at world 2 it has no byte advantage and loses

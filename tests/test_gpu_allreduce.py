@@ -196,7 +196,7 @@ def _worker(rank, world, port, q):
         comm.check()
 
         # DDP comm hook vs stock DDP on the same model / data: 3 steps, identical parameters
-        def run(use_hook, nvls_buckets=False):
+        def run(use_hook, nvls_buckets=False, cpp_hook=False):
             torch.manual_seed(0)
             model = torch.nn.Sequential(torch.nn.Linear(512, 2048), torch.nn.ReLU(), torch.nn.Linear(2048, 4096),
                                         torch.nn.ReLU(), torch.nn.Linear(4096, 512)).cuda()
@@ -204,7 +204,7 @@ def _worker(rank, world, port, q):
             hook_state = None
             if use_hook:
                 hook_state = register_p2p_comm_hook(ddp, comm=comm, zero_copy_min_bytes=1 << 20,
-                                                    nvls_buckets=nvls_buckets)
+                                                    nvls_buckets=nvls_buckets, cpp_hook=cpp_hook)
             opt = torch.optim.SGD(ddp.parameters(), lr=0.1)
             g = torch.Generator(device="cuda").manual_seed(1234 + rank)
             for _ in range(5):  # long enough for the buckets to be registered (zero-copy) on step 3
@@ -215,9 +215,22 @@ def _worker(rank, world, port, q):
                 assert hook_state._registered, "no bucket was registered for zero-copy"
                 kinds = {("nvls" if r[3] is not None else "ipc") for r in hook_state._registered.values()}
                 results[("hook_bucket_paths", tuple(sorted(kinds)))] = True
+                if cpp_hook:  # registered buckets must have been served by the C++ fast path
+                    h = hook_state.cpp_handle
+                    results[("cpp_hook_fast_calls", h.fast_calls, h.slow_calls)] = h.fast_calls > 0
             return [p.detach().clone() for p in model.parameters()]
 
         a, b = run(True), run(False)
+        # C++ comm hook (csrc_torch/ddp_hook.cpp): same buckets, no interpreter on the fast path
+        from distributed_llms_example_b200.comm import _load_cpp_hook
+
+        if _load_cpp_hook() is not None:
+            d = run(True, cpp_hook=True)
+            results[("cpp_hook_bit_identical_to_python_hook", True)] = all(torch.equal(x, y) for x, y in zip(d, a))
+            if nvls_ok:
+                e = run(True, nvls_buckets=True, cpp_hook=True)
+                excess = max(float(((x - y).abs() - 1e-5 * y.abs()).max()) for x, y in zip(e, b))
+                results[("cpp_hook_nvls_buckets_match_stock", excess)] = excess < 1e-7
         if nvls_ok:
             # same model with the Reducer's buckets placed in the multicast-bound region
             c = run(True, nvls_buckets=True)

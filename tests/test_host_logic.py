@@ -431,3 +431,66 @@ def test_synthetic_features_are_deterministic_per_rank_and_shaped_like_the_scrip
         assert -100 not in f["labels"]  # REF mode: what the scripts really feed
     m = make_features(3, rank=0, label_mode="MASK")
     assert all(8 < len(f["labels"]) <= 128 and f["labels"][-1] == 1 for f in m)  # ragged, eos-terminated
+
+
+# ---- C++ DDP comm hook: attach + delegation to the Python hook, on CPU over gloo ----------------
+def _cpp_hook_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from distributed_llms_example_b200.build import build_hook
+        from distributed_llms_example_b200.comm import _load_cpp_hook
+
+        build_hook()
+        mod = _load_cpp_hook()
+        calls = []
+
+        def mean_hook(state, bucket: dist.GradBucket) -> torch.futures.Future[torch.Tensor]:
+            calls.append(bucket.index())
+            buf = bucket.buffer()
+            buf.div_(world)
+            return dist.all_reduce(buf, async_op=True).get_future().then(lambda f: f.value()[0])
+
+        def run(cpp):
+            torch.manual_seed(0)
+            model = torch.nn.Sequential(torch.nn.Linear(32, 64), torch.nn.ReLU(), torch.nn.Linear(64, 8))
+            ddp = torch.nn.parallel.DistributedDataParallel(model)
+            handle = None
+            if cpp:  # no bucket is ever entered in the table: every call takes the delegation path
+                handle = mod.attach(ddp.reducer, mean_hook, None, 0, 0, 0, 1.0 / world, 0, 0)
+            opt = torch.optim.SGD(ddp.parameters(), lr=0.1)
+            g = torch.Generator().manual_seed(1234 + rank)
+            for _ in range(3):
+                ddp(torch.randn(4, 32, generator=g)).square().mean().backward()
+                opt.step(); opt.zero_grad()
+            return torch.cat([p.detach().reshape(-1) for p in model.parameters()]), handle
+
+        a, handle = run(True)
+        b, _ = run(False)
+        ok = bool(torch.allclose(a, b, rtol=1e-6, atol=1e-8)) and len(calls) >= 3
+        ok = ok and handle.slow_calls == len(calls) and handle.fast_calls == 0
+        handle.set_entry(5, 0x1000, 16, 1, 4096)  # table grows on demand
+        q.put((rank, ok, None))
+    except Exception:
+        import traceback
+
+        q.put((rank, False, traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_cpp_comm_hook_attaches_and_delegates_to_python_hook():
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_cpp_hook_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    outs = [q.get(timeout=600) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, ok, err in outs:
+        assert err is None, f"rank {rank}:\n{err}"
+        assert ok
