@@ -281,6 +281,7 @@ def _vote_worker(rank, world, port, q):
             st.comm = _FakeComm(rank, world, exportable)
             st.zero_copy, st.zero_copy_min_bytes = True, 1 << 20
             st._last_seen, st._registered = {}, {}
+            st.cpp_handle = None
             return st
 
         big = 1 << 20  # elements -> 4 MiB
