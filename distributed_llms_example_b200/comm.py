@@ -422,19 +422,32 @@ def _load_cpp_hook():
 def register_p2p_comm_hook(ddp_model, state: Optional[HookState] = None, **comm_kwargs) -> HookState:
     """Attach the peer-memory all-reduce to a DDP module; collective on first use.
 
-    With ``cpp_hook=True`` (or ``B2_CPP_HOOK=1``) the Reducer gets the C++ hook of
-    csrc_torch/ddp_hook.cpp, which serves registered buckets without touching the interpreter and
-    delegates everything else to ``p2p_allreduce_hook``; otherwise the Python hook is registered
-    through ``ddp_model.register_comm_hook``."""
+    By default (``B2_CPP_HOOK=auto``) the Reducer gets the C++ hook of csrc_torch/ddp_hook.cpp when
+    that extension has been built and loads: it serves registered buckets without touching the
+    interpreter and delegates everything else to ``p2p_allreduce_hook``. ``cpp_hook=False`` /
+    ``B2_CPP_HOOK=0``, or an extension that is missing or fails to load, registers the Python hook
+    through ``ddp_model.register_comm_hook`` (same kernels, ~15 us more host time per bucket);
+    ``cpp_hook=True`` / ``B2_CPP_HOOK=1`` makes a missing extension an error."""
     nvls_buckets = comm_kwargs.pop("nvls_buckets", None)
     cpp_hook = comm_kwargs.pop("cpp_hook", None)
     state = state or HookState(**comm_kwargs)
+    required = cpp_hook is True
     if cpp_hook is None:
-        cpp_hook = os.environ.get("B2_CPP_HOOK", "0") == "1"
-    mod = _load_cpp_hook() if cpp_hook else None
-    if cpp_hook and mod is None:
-        raise RuntimeError("B2_CPP_HOOK=1 but _b2ddp_hook.so is not built "
-                           "(python -m distributed_llms_example_b200.build)")
+        env = os.environ.get("B2_CPP_HOOK", "auto")
+        cpp_hook, required = env != "0", env == "1"
+    mod = None
+    if cpp_hook:
+        try:
+            mod = _load_cpp_hook()
+        except Exception as exc:  # e.g. built against another torch: fall back to the Python hook
+            if required:
+                raise
+            import warnings
+
+            warnings.warn(f"b200: C++ DDP hook could not be loaded ({exc}); using the Python hook")
+        if mod is None and required:
+            raise RuntimeError("the C++ DDP hook was requested but _b2ddp_hook.so is not built "
+                               "(python -m distributed_llms_example_b200.build)")
     if mod is not None:
         lib = state.comm._lib
         fn_reg = C.cast(lib.b2_allreduce_registered, C.c_void_p).value
