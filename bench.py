@@ -321,24 +321,37 @@ def main():
            "clocks": clocks.summary(), "roofline": roofline, "final_loss": last_loss,
            "params": n_params, "lib": str(_lib.lib_path().name) if args.impl == "b200" else None}
     if world > 1:
-        out["grad_sync"] = grad_sync_probe(h, args.impl, world)
-        if h.hook_state is not None:  # which path the Reducer's buckets actually took
-            regs = h.hook_state._registered.values()
-            out["grad_sync"]["ddp_buckets"] = {
-                "reduced_per_step": h.hook_state.total_buckets_reduced // max(1, h.steps_done),
-                "cpp_hook": h.hook_state.cpp_handle is not None,
-                "nvls_in_place": sum(1 for r in regs if r[3] is not None),
-                "ipc_push_in_place": sum(1 for r in regs if r[3] is None),
-            }
-    h.close()
-
-    if rank == 0 and world == 1 and not args.no_cpu_baseline and args.impl == "b200":
-        sps, threads, sample, _ = run_cpu(args, args.cpu_steps, 1)
-        out["cpu_baseline"] = {"value": sps, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample}
-    if rank == 0:
-        print(json.dumps(out), flush=True)
+        # optional extras must never cost the headline numbers above
+        try:
+            out["grad_sync"] = grad_sync_probe(h, args.impl, world)
+            if h.hook_state is not None:  # which path the Reducer's buckets actually took
+                regs = h.hook_state._registered.values()
+                out["grad_sync"]["ddp_buckets"] = {
+                    "reduced_per_step": h.hook_state.total_buckets_reduced // max(1, h.steps_done),
+                    "cpp_hook": h.hook_state.cpp_handle is not None,
+                    "nvls_in_place": sum(1 for r in regs if r[3] is not None),
+                    "ipc_push_in_place": sum(1 for r in regs if r[3] is None),
+                }
+        except Exception as exc:  # collective: every rank takes the same branch or the run hangs
+            out["grad_sync"] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
     if world > 1:
-        dist.destroy_process_group()
+        # the line goes out before any teardown (unmapping peers, destroying the process group)
+        if rank == 0:
+            print(json.dumps(out), flush=True)
+        try:
+            h.close()
+        finally:
+            dist.destroy_process_group()
+        return
+    h.close()
+    if not args.no_cpu_baseline and args.impl == "b200":
+        try:
+            sps, threads, sample, _ = run_cpu(args, args.cpu_steps, 1)
+            out["cpu_baseline"] = {"value": sps, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample}
+        except Exception as exc:
+            out["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
+                                   "sample": f"failed: {type(exc).__name__}: {exc}"[:300]}
+    print(json.dumps(out), flush=True)
 
 
 if __name__ == "__main__":
