@@ -72,9 +72,15 @@ SIGNATURES = {
     "b2_pool_free": (None, [_vp, C.c_ssize_t, C.c_int, _vp]),
     "b2_allreduce_nvls_inplace": (C.c_int, [_vp, C.c_uint64, _i64, _f32, _vp]),
     "b2_comm_status": (C.c_int, [_vp]),
+    "b2_comm_poll": (C.c_int, [_vp]),
+    "b2_comm_status_word": (_vp, [_vp]),
+    "b2_comm_sumsq_enable": (C.c_int, [_vp, _i32]),
+    "b2_comm_sumsq_numel": (_i64, [_vp]),
+    "b2_comm_sumsq_clip": (C.c_int, [_vp, _f32, _vp, _vp, _vp]),
     "b2_comm_destroy": (C.c_int, [_vp]),
     "b2_allreduce_emulated_scratch_bytes": (_sz, [_i32, _i64]),
     "b2_allreduce_emulated": (C.c_int, [C.POINTER(_vp), _i32, _i64, _i32, _f32, _i32, _vp, _vp]),
+    "b2_allreduce_emulated_sumsq": (C.c_int, [C.POINTER(_vp), _i32, _i64, _i32, _f32, _i32, _vp, _vp, _vp]),
 }
 
 _lock = threading.Lock()
@@ -96,11 +102,13 @@ def load() -> C.CDLL:
             return _lib
         try:
             path = build()
-        except Exception as exc:  # no nvcc on this machine: accept a prebuilt library only
-            if not LIB_PATH.exists():
+        except Exception as exc:
+            # Only a machine WITHOUT nvcc may run a prebuilt library whose sources it cannot check;
+            # a compile or link error is never papered over with a stale .so.
+            if "nvcc not found" not in str(exc) or not LIB_PATH.exists():
                 raise ImportError(
-                    f"libb2ddp.so is missing and could not be built ({exc}); this package has no "
-                    "CPU fallback — run `python -m distributed_llms_example_b200.build`") from exc
+                    f"libb2ddp.so could not be built ({exc}); this package has no CPU fallback — "
+                    "run `python -m distributed_llms_example_b200.build --verbose`") from exc
             path = LIB_PATH
         lib = C.CDLL(str(path))
         for name, (res, args) in SIGNATURES.items():

@@ -52,11 +52,45 @@ def _fingerprint() -> str:
     return h.hexdigest()
 
 
+class _BuildLock:
+    """Inter-process lock (flock on a file next to the library): under torchrun every rank imports
+    the package at once, and only one of them may run nvcc into build/ and replace the library."""
+
+    def __init__(self, path: Path):
+        self.path, self.fd = path, None
+
+    def __enter__(self):
+        import fcntl
+
+        self.fd = os.open(str(self.path), os.O_CREAT | os.O_RDWR, 0o644)
+        fcntl.flock(self.fd, fcntl.LOCK_EX)
+        return self
+
+    def __exit__(self, *exc):
+        import fcntl
+
+        fcntl.flock(self.fd, fcntl.LOCK_UN)
+        os.close(self.fd)
+
+
+def _up_to_date(fp: str) -> bool:
+    return LIB_PATH.exists() and _STAMP.exists() and _STAMP.read_text() == fp
+
+
 def build(force: bool = False, verbose: bool = False) -> Path:
-    """Compile every csrc/*.cu and link libb2ddp.so; no-op when sources are unchanged."""
+    """Compile every csrc/*.cu and link libb2ddp.so; no-op when sources are unchanged. Safe to call
+    from several processes at once: one compiles (into a temporary name, renamed atomically), the
+    others wait on the lock and find the finished library."""
     fp = _fingerprint()
-    if not force and LIB_PATH.exists() and _STAMP.exists() and _STAMP.read_text() == fp:
+    if not force and _up_to_date(fp):
         return LIB_PATH
+    with _BuildLock(PKG_DIR / ".build.lock"):
+        if not force and _up_to_date(fp):  # another process built it while this one waited
+            return LIB_PATH
+        return _build_locked(fp, verbose)
+
+
+def _build_locked(fp: str, verbose: bool) -> Path:
     nvcc = _nvcc()
     obj_dir = PKG_DIR / "build"
     obj_dir.mkdir(exist_ok=True)
@@ -76,10 +110,14 @@ def build(force: bool = False, verbose: bool = False) -> Path:
             print(out, file=sys.stderr)
         if p.returncode != 0:
             raise RuntimeError(f"nvcc failed on {src.name}:\n{out}")
-    link = [nvcc, "-shared", "-cudart", "static", "-o", str(LIB_PATH), *map(str, objs)]
+    tmp = LIB_PATH.with_suffix(f".so.tmp{os.getpid()}")
+    link = [nvcc, "-shared", "-cudart", "static", "-o", str(tmp), *map(str, objs)]
     r = subprocess.run(link, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}")
+    if _STAMP.exists():
+        _STAMP.unlink()  # never a valid stamp next to a library it does not describe
+    os.replace(tmp, LIB_PATH)  # atomic: a process that CDLLs concurrently sees the old or the new file, whole
     _STAMP.write_text(fp)
     return LIB_PATH
 
@@ -101,14 +139,19 @@ def build_hook(force: bool = False, verbose: bool = False) -> Path:
         raise RuntimeError(f"torch is required to build the DDP hook: {exc}")
     if not force and HOOK_LIB.exists() and stamp.exists() and stamp.read_text() == fp:
         return HOOK_LIB
-    import torch.utils.cpp_extension as ce
+    with _BuildLock(PKG_DIR / ".build.lock"):
+        if not force and HOOK_LIB.exists() and stamp.exists() and stamp.read_text() == fp:
+            return HOOK_LIB
+        import torch.utils.cpp_extension as ce
 
-    bdir = PKG_DIR / "build" / "hook"
-    bdir.mkdir(parents=True, exist_ok=True)
-    ce.load(name="_b2ddp_hook", sources=[str(HOOK_SRC)], extra_cflags=["-O2", "-std=c++17"], with_cuda=True,
-            build_directory=str(bdir), verbose=verbose, is_python_module=False)
-    shutil.copy2(bdir / "_b2ddp_hook.so", HOOK_LIB)
-    stamp.write_text(fp)
+        bdir = PKG_DIR / "build" / "hook"
+        bdir.mkdir(parents=True, exist_ok=True)
+        ce.load(name="_b2ddp_hook", sources=[str(HOOK_SRC)], extra_cflags=["-O2", "-std=c++17"], with_cuda=True,
+                build_directory=str(bdir), verbose=verbose, is_python_module=False)
+        tmp = HOOK_LIB.with_suffix(f".so.tmp{os.getpid()}")
+        shutil.copy2(bdir / "_b2ddp_hook.so", tmp)
+        os.replace(tmp, HOOK_LIB)
+        stamp.write_text(fp)
     return HOOK_LIB
 
 

@@ -15,6 +15,7 @@ barriers); only gradient bytes move through libb2ddp's kernels. Single node, wor
 """
 import ctypes as C
 import os
+import weakref
 from typing import Optional
 
 import torch
@@ -23,7 +24,21 @@ import torch.distributed as dist
 from . import _lib
 
 __all__ = ["P2PComm", "HookState", "p2p_allreduce_hook", "register_p2p_comm_hook",
-           "average_gradients", "exchange_handles", "default_comm"]
+           "average_gradients", "exchange_handles", "default_comm", "poll_all", "live_comms"]
+
+_LIVE: "weakref.WeakSet[P2PComm]" = weakref.WeakSet()
+
+
+def live_comms() -> list:
+    return [c for c in list(_LIVE) if c._ctx is not None]
+
+
+def poll_all() -> None:
+    """Raise B2Error(B2_ERR_TIMEOUT) if any live communicator of this process has seen a peer miss
+    a barrier. One host load per communicator, no synchronisation: AdamW.step() calls this every
+    step so that a poisoned (NaN-filled) gradient is never applied silently."""
+    for c in live_comms():
+        c.poll()
 
 _WIRE = {"fp32": _lib.B2_F32, "bf16": _lib.B2_BF16}
 _ALGO = {"auto": _lib.B2_ALGO_AUTO, "one_shot": _lib.B2_ALGO_ONE_SHOT, "two_shot": _lib.B2_ALGO_TWO_SHOT}
@@ -67,7 +82,11 @@ class P2PComm:
             staging_bytes = int(os.environ.get("B2_AR_STAGING_MB", "64")) << 20
         self._lib = _lib.load()
         self._ctx = C.c_void_p()
+        self._hook_states: "weakref.WeakSet[HookState]" = weakref.WeakSet()
+        self.sumsq_enabled = False
         _lib.check(self._lib.b2_comm_create(self.rank, self.world, staging_bytes, C.byref(self._ctx)))
+        self._c_poll = self._lib.b2_comm_poll
+        _LIVE.add(self)
         if self.world > 1:
             raw = C.create_string_buffer(_lib.B2_IPC_HANDLE_BYTES)
             _lib.check(self._lib.b2_comm_get_handle(self._ctx, raw))
@@ -254,24 +273,52 @@ class P2PComm:
         """Synchronising health check: raises if a kernel timed out waiting for a peer."""
         _lib.check(self._lib.b2_comm_status(self._ctx))
 
+    def poll(self) -> None:
+        """Non-synchronising health check (one host load of the mapped status word). A rank that
+        waits longer than B2_AR_TIMEOUT_MS for a peer poisons the communicator on EVERY rank: the
+        buckets reduced from then on are NaN-filled and this raises B2Error(B2_ERR_TIMEOUT)."""
+        if self._ctx is not None:
+            rc = self._c_poll(self._ctx)
+            if rc != 0:
+                _lib.check(rc)
+
+    # -- sum of squares folded into the all-reduce (gradient-clipping fold-in, SURVEY.md 8f row 1) --
+    def enable_sumsq(self, on: bool = True) -> None:
+        """From the next all-reduce on, every bucket also accumulates sum(x*x) of its reduced values
+        (identical on every rank). All ranks must switch at the same point of the program."""
+        _lib.check(self._lib.b2_comm_sumsq_enable(self._ctx, 1 if on else 0))
+        self.sumsq_enabled = bool(on)
+
+    def sumsq_numel(self) -> int:
+        return int(self._lib.b2_comm_sumsq_numel(self._ctx))
+
+    def sumsq_clip_(self, max_norm: float, out: torch.Tensor, *, stream: Optional[torch.cuda.Stream] = None) -> None:
+        """out[0] = sqrt(total), out[1] = min(1, max_norm / (out[0] + 1e-6)); resets the total. The
+        stream must be ordered after the all-reduces (it is, after DDP's finalize_backward)."""
+        s = (stream or torch.cuda.current_stream(self.device)).cuda_stream
+        _lib.check(self._lib.b2_comm_sumsq_clip(self._ctx, float(max_norm), out.data_ptr(), out.data_ptr() + 4, s))
+        _lib.count_launch()
+
     def close(self) -> None:
+        """Collective. Detaches every DDP hook that still points at this communicator first (a later
+        backward on such a DDP module raises instead of touching freed memory), then unmaps."""
         if self._ctx is not None:
             torch.cuda.synchronize(self.device)
             if self.world > 1 and dist.is_initialized():
                 dist.barrier(self.group)  # nobody unmaps while a peer may still read
+            for st in list(self._hook_states):
+                st.invalidate()
+            for key in [k for k, p in _rebuild_pools.items() if p is self._pool]:
+                _rebuild_pools.pop(key, None)
             self._lib.b2_comm_destroy(self._ctx)
             self._ctx = None
         global _default
         if _default is self:
             _default = None
 
-    def __del__(self):  # best effort; explicit close() is the collective-safe way
-        try:
-            if getattr(self, "_ctx", None) is not None:
-                self._lib.b2_comm_destroy(self._ctx)
-                self._ctx = None
-        except Exception:
-            pass
+    # No __del__: destroying without the barrier of close() could unmap memory a peer is still
+    # reading, and a C++ hook may still hold the raw pointer. An unclosed communicator is reclaimed
+    # at process exit.
 
 
 _default: Optional["P2PComm"] = None
@@ -310,8 +357,26 @@ class HookState:
         self.zero_copy_min_bytes = zero_copy_min_bytes
         self._last_seen: dict[int, tuple] = {}    # bucket index -> (data_ptr, numel) at its last call
         self._registered: dict[int, tuple] = {}   # bucket index -> (data_ptr, numel, reg_id | None, nvls offset | None)
+        self._attempts: dict[int, int] = {}       # bucket index -> failed collective votes so far
+        self._never: set[int] = set()             # buckets every rank agreed to leave on the staging path
+        self.max_attempts = int(os.environ.get("B2_AR_REGISTER_ATTEMPTS", "3"))
         self._c_allreduce_nvls_inplace = self.comm._lib.b2_allreduce_nvls_inplace
         self.cpp_handle = None  # set when the C++ hook serves the registered buckets
+        self.closed = False
+        self.comm._hook_states.add(self)
+
+    def invalidate(self) -> None:
+        """Called by P2PComm.close(): the hook must not touch the communicator any more."""
+        self.closed = True
+        if self.cpp_handle is not None:
+            self.cpp_handle.close()
+        for reg in self._registered.values():
+            if reg[2] is not None and self.comm._ctx is not None:
+                try:
+                    self.comm.unregister(reg[2])
+                except _lib.B2Error:
+                    pass
+        self._registered.clear()
 
     @property
     def total_buckets_reduced(self) -> int:
@@ -329,18 +394,38 @@ class HookState:
                     f"DDP bucket {index} moved after it was registered for peer access "
                     f"({reg[:2]} -> {key}); rebuild the HookState (or set B2_AR_ZERO_COPY=0)")
             return reg
-        if not self.zero_copy or buf.numel() * 4 < self.zero_copy_min_bytes:
+        if not self.zero_copy or buf.numel() * 4 < self.zero_copy_min_bytes or index in self._never:
             return None
         stable = self._last_seen.get(index) == key
         self._last_seen[index] = key
         nvls_off = self.comm.nvls_offset(buf) if hasattr(self.comm, "nvls_offset") else None
+        exportable = True
         try:
             mine = (stable,) + (self.comm.export(buf) if nvls_off is None else (b"", 0)) + (nvls_off,)
         except _lib.B2Error:
-            mine = (False, b"", 0, None)  # memory that cannot be exported (e.g. expandable segments)
+            exportable = False  # memory that cannot be exported (e.g. expandable segments)
+            mine = (False, b"", 0, None)
+        # Every rank contributes (stable, handle, offset, nvls offset, exportable, attempts so far)
+        # and draws the SAME conclusion from the gathered votes, including "give up": a bucket that
+        # cannot be exported anywhere, or that has failed max_attempts votes, gets a permanent
+        # negative entry, so that a run on an allocator setting that defeats the zero-copy path
+        # pays for a few collectives at start-up instead of one per bucket per step for ever.
+        attempts = self._attempts.get(index, 0)
         votes: list = [None] * self.comm.world
-        dist.all_gather_object(votes, mine, group=self.comm.group)
+        dist.all_gather_object(votes, mine + (exportable, attempts), group=self.comm.group)
+
+        def give_up_or_retry():
+            self._attempts[index] = attempts + 1
+            if (not all(v[4] for v in votes)) or max(v[5] for v in votes) + 1 >= self.max_attempts:
+                self._never.add(index)
+            return None
+
         if not all(v[0] for v in votes):
+            # "not stable yet" is normal for the first sighting; it only counts as a failed attempt
+            # once the bucket has been seen before everywhere
+            if attempts > 0 or not all(v[4] for v in votes):
+                return give_up_or_retry()
+            self._attempts[index] = 1
             return None
         offs = {v[3] for v in votes}
         if len(offs) == 1 and nvls_off is not None:
@@ -348,9 +433,22 @@ class HookState:
             # the switch reduces it in place, nothing to map
             reg = key + (None, nvls_off)
         elif None in offs and len(offs) == 1:
-            reg = key + (self.comm.register(buf, peers=[(v[1], v[2]) for v in votes]), None)
+            # mapping can fail on one rank only (e.g. out of address space): vote again so that all
+            # ranks either use the registration or fall back together
+            try:
+                reg_id = self.comm.register(buf, peers=[(v[1], v[2]) for v in votes])
+            except _lib.B2Error:
+                reg_id = None
+            oks: list = [None] * self.comm.world
+            dist.all_gather_object(oks, reg_id is not None, group=self.comm.group)
+            if not all(oks):
+                if reg_id is not None:
+                    self.comm.unregister(reg_id)
+                self._never.add(index)
+                return None
+            reg = key + (reg_id, None)
         else:
-            return None  # mixed placement across ranks: stay on the staging path
+            return give_up_or_retry()  # mixed placement across ranks: stay on the staging path
         self._registered[index] = reg
         if self.cpp_handle is not None:  # from now on the C++ hook handles this bucket by itself
             self.cpp_handle.set_entry(index, reg[0], reg[1], 1 if reg[3] is not None else 0,
@@ -371,6 +469,9 @@ def p2p_allreduce_hook(state: HookState, bucket: dist.GradBucket) -> torch.futur
     waits on - no host synchronisation anywhere.
     """
     comm = state.comm
+    if state.closed or comm._ctx is None:
+        raise RuntimeError("b200 DDP hook: its communicator has been closed; rebuild the DDP module's hook")
+    comm.poll()  # a peer that missed a barrier earlier: raise here, on every rank, not train on NaN
     buf = bucket.buffer()
     side = state.stream
     producer = torch.cuda.current_stream(comm.device)
@@ -453,9 +554,13 @@ def register_p2p_comm_hook(ddp_model, state: Optional[HookState] = None, **comm_
         fn_reg = C.cast(lib.b2_allreduce_registered, C.c_void_p).value
         fn_nvls = C.cast(lib.b2_allreduce_nvls_inplace, C.c_void_p).value
         side = state.stream
+        ddp_model._check_comm_hook(p2p_allreduce_hook)  # the checks DDP.register_comm_hook makes
+        status_word = lib.b2_comm_status_word(state.comm._ctx) or 0
         state.cpp_handle = mod.attach(ddp_model.reducer, p2p_allreduce_hook, state, state.comm._ctx.value, fn_reg,
-                                      fn_nvls, state.scale, state.comm.device.index, side.stream_id)
-        ddp_model._comm_hooks.append((p2p_allreduce_hook, state))  # what DDP.register_comm_hook records
+                                      fn_nvls, state.scale, state.comm.device.index, side.stream_id, status_word)
+        # ... and its bookkeeping (distributed.py:2064-2067): the hook list and the logger's hook name
+        ddp_model.logger._set_comm_hook_name(p2p_allreduce_hook.__qualname__)
+        ddp_model._comm_hooks.append((p2p_allreduce_hook, state))
     else:
         ddp_model.register_comm_hook(state, p2p_allreduce_hook)
     if nvls_buckets is None:
@@ -519,6 +624,7 @@ def average_gradients(model: torch.nn.Module, comm: Optional[P2PComm] = None) ->
     the gradients and with the ``optimizer.step()`` that follows at train-task.py:295.
     """
     comm = comm or default_comm()
+    comm.poll()  # raises if an earlier exchange was poisoned by a missing peer
     grads = [p.grad for p in model.parameters()]  # the reference dereferences every .grad too
     if any(g is None for g in grads):
         raise AttributeError("average_gradients: a parameter has no .grad (train-task.py:68 would fail too)")

@@ -35,6 +35,7 @@ template <int W>
 __global__ void __launch_bounds__(32, 1)
 gate_kernel(const __grid_constant__ ArArgs<1> args, uint32_t epoch, unsigned long long timeout_ns) {
   const RankView& v = args.v[0];
+  int bad = 0;
   if (threadIdx.x < W) {
     const int peer = threadIdx.x;
     uint32_t* gate_peer = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(v.flags[peer]) + kGateOff);
@@ -44,13 +45,15 @@ gate_kernel(const __grid_constant__ ArArgs<1> args, uint32_t epoch, unsigned lon
     unsigned spins = 0;
     while ((int)(ld_relaxed_sys(gate_mine + peer) - epoch) < 0) {
       __nanosleep(100);
-      if ((++spins & 1023u) == 0 && globaltimer_ns() - t0 > timeout_ns) {
-        atomicExch(v.status, 1u);
-        break;
+      if ((++spins & 255u) == 0) {
+        if (comm_poisoned(v)) { bad = 1; break; }
+        if (globaltimer_ns() - t0 > timeout_ns) { bad = 2; break; }
       }
     }
     fence_acquire_sys();
   }
+  // the data kernel behind this gate sees the raised status word and poisons its bucket
+  if (__any_sync(0xffffffffu, bad) && threadIdx.x == 0) raise_timeout<W>(v);
 }
 
 template <int W, bool BF16W>
@@ -75,6 +78,7 @@ allreduce_kernel(const __grid_constant__ ArArgs<NV> args, long long numel, float
                  uint32_t epoch, unsigned long long timeout_ns) {
   using Wr = Wire<BF16W>;
   constexpr int EPP = Wr::kElems;
+  constexpr bool kOneShot = (ALGO == B2_ALGO_ONE_SHOT || W == 1);
   const RankView& v = args.v[NV == 1 ? 0 : blockIdx.y];
   const int rank = v.rank;
   const int nb = gridDim.x, b = blockIdx.x, tid = threadIdx.x;
@@ -84,8 +88,10 @@ allreduce_kernel(const __grid_constant__ ArArgs<NV> args, long long numel, float
   // Elements past the last whole pack ride in block 0, one-shot style, for both algorithms.
   const long long tail0 = npack * EPP;
   char* own_tail = own + npack * 16;
+  float sq = 0.f;  // squares of the reduced values this thread produced (v.sumsq)
 
-  if (ALGO == B2_ALGO_ONE_SHOT || W == 1) {
+  if (comm_poisoned(v)) { poison_local(v, numel); return; }
+  if (kOneShot) {
     const long long c = (npack + nb - 1) / nb;
     const long long lo = min((long long)b * c, npack), hi = min(lo + c, npack);
     {
@@ -102,7 +108,7 @@ allreduce_kernel(const __grid_constant__ ArArgs<NV> args, long long numel, float
         *reinterpret_cast<uint4*>(own + i * 16) = Wr::load_scaled(buf, i, scale);
     }
     if (b == 0 && tid < numel - tail0) Wr::tail_store(own_tail, tid, Wr::stage1(buf, tail0 + tid, scale));
-    cross_barrier<W>(v, epoch, timeout_ns);
+    if (!cross_barrier<W>(v, epoch, timeout_ns)) { poison_local(v, numel); return; }
     constexpr int U = (W >= 8) ? 2 : 4;
     long long i = lo + tid;
     for (; i + (U - 1) * kArThreads < hi; i += U * kArThreads) {
@@ -110,12 +116,18 @@ allreduce_kernel(const __grid_constant__ ArArgs<NV> args, long long numel, float
 #pragma unroll
       for (int u = 0; u < U; ++u) reduce_packs<W, BF16W>(v, i + u * kArThreads, acc[u]);
 #pragma unroll
-      for (int u = 0; u < U; ++u) Wr::store_buf(buf, i + u * kArThreads, Wr::from_f(acc[u]));
+      for (int u = 0; u < U; ++u) {
+        const uint4 o = Wr::from_f(acc[u]);
+        sq += Wr::sq(o);
+        Wr::store_buf(buf, i + u * kArThreads, o);
+      }
     }
     for (; i < hi; i += kArThreads) {
       float acc[EPP];
       reduce_packs<W, BF16W>(v, i, acc);
-      Wr::store_buf(buf, i, Wr::from_f(acc));
+      const uint4 o = Wr::from_f(acc);
+      sq += Wr::sq(o);
+      Wr::store_buf(buf, i, o);
     }
   } else {
     const long long Q = (npack + W - 1) / W;   // packs per rank slice
@@ -139,7 +151,7 @@ allreduce_kernel(const __grid_constant__ ArArgs<NV> args, long long numel, float
         *reinterpret_cast<uint4*>(own + i * 16) = Wr::load_scaled(buf, i, scale);
     }
     if (b == 0 && tid < numel - tail0) Wr::tail_store(own_tail, tid, Wr::stage1(buf, tail0 + tid, scale));
-    cross_barrier<W>(v, epoch, timeout_ns);
+    if (!cross_barrier<W>(v, epoch, timeout_ns)) { poison_local(v, numel); return; }
     // reduce-scatter: my slice, my sub-range, summed over all ranks; publish in place.
     {
       const long long slo = min((long long)rank * Q, npack), shi = min(slo + Q, npack);
@@ -153,6 +165,7 @@ allreduce_kernel(const __grid_constant__ ArArgs<NV> args, long long numel, float
 #pragma unroll
         for (int u = 0; u < U; ++u) {
           const uint4 o = Wr::from_f(acc[u]);
+          sq += Wr::sq(o);
           *reinterpret_cast<uint4*>(own + (i + u * kArThreads) * 16) = o;
           Wr::store_buf(buf, i + u * kArThreads, o);
         }
@@ -161,11 +174,37 @@ allreduce_kernel(const __grid_constant__ ArArgs<NV> args, long long numel, float
         float acc[EPP];
         reduce_packs<W, BF16W>(v, i, acc);
         const uint4 o = Wr::from_f(acc);
+        sq += Wr::sq(o);
         *reinterpret_cast<uint4*>(own + i * 16) = o;
         Wr::store_buf(buf, i, o);
       }
     }
-    cross_barrier<W>(v, epoch + 1, timeout_ns);
+  }
+  // tail elements (fewer than one pack): every rank sums them itself after the first barrier;
+  // their squares are counted once (one-shot: by every rank for itself; two-shot: by rank 0)
+  if (b == 0 && tid < numel - tail0) {
+    float acc = 0.f;
+#pragma unroll
+    for (int k = 0; k < W; ++k) {
+      const float x = Wr::tail_load(v.stage[k] + npack * 16, tid);
+      acc = (k == 0) ? x : __fadd_rn(acc, x);
+    }
+    acc = Wr::round_wire(acc);
+    buf[tail0 + tid] = acc;
+    if (kOneShot || rank == 0) sq = __fmaf_rn(acc, acc, sq);
+  }
+  if (kOneShot) {
+    if (v.sumsq) {
+      block_sumsq<W>(v, sq, false);
+      fold_sumsq(v, rank, 1);
+    }
+    return;
+  }
+  if (v.sumsq) block_sumsq<W>(v, sq, true);
+  if (!cross_barrier<W>(v, epoch + 1, timeout_ns)) { poison_local(v, numel); return; }
+  {
+    const long long Q = (npack + W - 1) / W;
+    const long long q = (Q + nb - 1) / nb;
     // all-gather: pull the other ranks' reduced sub-ranges, starting with my right-hand
     // neighbour so that the W ranks do not all hit the same peer at the same time.
     constexpr int U2 = 4;
@@ -186,16 +225,7 @@ allreduce_kernel(const __grid_constant__ ArArgs<NV> args, long long numel, float
       for (; i < hi; i += kArThreads) Wr::store_buf(buf, i, ld_peer16(src + i * 16));
     }
   }
-  // tail elements (fewer than one pack): every rank sums them itself after the first barrier
-  if (b == 0 && tid < numel - tail0) {
-    float acc = 0.f;
-#pragma unroll
-    for (int k = 0; k < W; ++k) {
-      const float x = Wr::tail_load(v.stage[k] + npack * 16, tid);
-      acc = (k == 0) ? x : __fadd_rn(acc, x);
-    }
-    buf[tail0 + tid] = Wr::round_wire(acc);
-  }
+  if (v.sumsq) fold_sumsq(v, 0, W);
 }
 
 
@@ -225,8 +255,13 @@ allreduce_inplace_kernel(const __grid_constant__ ArArgs<NV> args, long long nume
   const long long Q = (npack + W - 1) / W;
   const long long q = (Q + nb - 1) / nb;
   constexpr int U = (W >= 8) ? 2 : 4;
+  float sq = 0.f;
 
-  if (!gated) cross_barrier<W>(v, epoch, timeout_ns);  // barrier A, unless a gate_kernel ran first
+  if (comm_poisoned(v)) { poison_local(v, numel); return; }
+  if (!gated && !cross_barrier<W>(v, epoch, timeout_ns)) {  // barrier A, unless a gate_kernel ran first
+    poison_local(v, numel);
+    return;
+  }
   {
     const long long slo = min((long long)rank * Q, npack), shi = min(slo + Q, npack);
     const long long lo = min(slo + (long long)b * q, shi), hi = min(lo + q, shi);
@@ -250,7 +285,9 @@ allreduce_inplace_kernel(const __grid_constant__ ArArgs<NV> args, long long nume
             acc[e] = (k == 0) ? t : __fadd_rn(acc[e], t);
           }
         }
-        *reinterpret_cast<uint4*>(buf + (i + u * kArThreads) * 4) = Wire<false>::from_f(acc);
+        const uint4 o = Wire<false>::from_f(acc);
+        sq += sq4(o);
+        *reinterpret_cast<uint4*>(buf + (i + u * kArThreads) * 4) = o;
       }
     }
     for (; i < hi; i += kArThreads) {
@@ -265,7 +302,9 @@ allreduce_inplace_kernel(const __grid_constant__ ArArgs<NV> args, long long nume
           acc[e] = (k == 0) ? t : __fadd_rn(acc[e], t);
         }
       }
-      *reinterpret_cast<uint4*>(buf + i * 4) = Wire<false>::from_f(acc);
+      const uint4 o = Wire<false>::from_f(acc);
+      sq += sq4(o);
+      *reinterpret_cast<uint4*>(buf + i * 4) = o;
     }
   }
   // tail (numel % 4): every rank sums it redundantly now, writes it after barrier B
@@ -277,8 +316,10 @@ allreduce_inplace_kernel(const __grid_constant__ ArArgs<NV> args, long long nume
       const float t = __fmul_rn(Wire<false>::tail_load(v.stage[k] + tail0 * 4, tid), scale);
       tail_acc = (k == 0) ? t : __fadd_rn(tail_acc, t);
     }
+    if (rank == 0) sq = __fmaf_rn(tail_acc, tail_acc, sq);
   }
-  cross_barrier<W>(v, epoch + 1, timeout_ns);
+  if (v.sumsq) block_sumsq<W>(v, sq, true);
+  if (!cross_barrier<W>(v, epoch + 1, timeout_ns)) { poison_local(v, numel); return; }
   if (has_tail) buf[tail0 + tid] = tail_acc;
   constexpr int U2 = 4;
 #pragma unroll 1
@@ -297,7 +338,8 @@ allreduce_inplace_kernel(const __grid_constant__ ArArgs<NV> args, long long nume
     }
     for (; i < hi; i += kArThreads) *reinterpret_cast<uint4*>(buf + i * 4) = ld_peer16(src + i * 16);
   }
-  cross_barrier<W>(v, epoch + 2, timeout_ns);
+  if (!cross_barrier<W>(v, epoch + 2, timeout_ns)) { poison_local(v, numel); return; }
+  if (v.sumsq) fold_sumsq(v, 0, W);
 }
 
 // ---- zero-copy, one pass: reduce my slice from every bucket, PUSH the result into every bucket --
@@ -314,27 +356,16 @@ allreduce_inplace_kernel(const __grid_constant__ ArArgs<NV> args, long long nume
 // bucket before it overwrites that element), so there is no hazard inside the pass.
 // Weak (fire-and-forget) 16-byte store: completion and visibility are established once, by the
 // __threadfence_system() + releasing flag store of the final barrier, not per store.
+// The owner holds every reduced element in registers, so the sum of squares the gradient clip
+// needs is folded into this pass: no separate read of the gradients.
 __device__ __forceinline__ void st_peer16(void* p, uint4 v) {
   asm volatile("st.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
                : "memory");
 }
 
-template <int W, int NV>
-__global__ void __launch_bounds__(kArThreads, 1)
-allreduce_push_kernel(const __grid_constant__ ArArgs<NV> args, long long numel, float scale,
-                      uint32_t epoch, unsigned long long timeout_ns, int gated) {
-  const RankView& v = args.v[NV == 1 ? 0 : blockIdx.y];
-  const int rank = v.rank;
-  const int nb = gridDim.x, b = blockIdx.x, tid = threadIdx.x;
-  const long long npack = numel / 4;
-  const long long tail0 = npack * 4;
-  const long long Q = (npack + W - 1) / W;
-  const long long q = (Q + nb - 1) / nb;
-  constexpr int U = (W >= 8) ? 2 : 4;
-
-  if (!gated) cross_barrier<W>(v, epoch, timeout_ns);
-  const long long slo = min((long long)rank * Q, npack), shi = min(slo + Q, npack);
-  const long long lo = min(slo + (long long)b * q, shi), hi = min(lo + q, shi);
+template <int W, int U>
+__device__ __forceinline__ void push_range(const RankView& v, long long lo, long long hi, float scale, float& sq) {
+  const int rank = v.rank, tid = threadIdx.x;
   long long i = lo + tid;
   for (; i + (U - 1) * kArThreads < hi; i += U * kArThreads) {
     uint4 r[U][W];
@@ -356,6 +387,7 @@ allreduce_push_kernel(const __grid_constant__ ArArgs<NV> args, long long numel, 
         }
       }
       const uint4 o = Wire<false>::from_f(acc);
+      sq += sq4(o);
 #pragma unroll
       for (int k = 0; k < W; ++k) st_peer16(v.stage[(rank + k) % W] + (i + u * kArThreads) * 16, o);
     }
@@ -373,9 +405,35 @@ allreduce_push_kernel(const __grid_constant__ ArArgs<NV> args, long long numel, 
       }
     }
     const uint4 o = Wire<false>::from_f(acc);
+    sq += sq4(o);
 #pragma unroll
     for (int k = 0; k < W; ++k) st_peer16(v.stage[(rank + k) % W] + i * 16, o);
   }
+}
+
+template <int W, int NV>
+__global__ void __launch_bounds__(kArThreads, 1)
+allreduce_push_kernel(const __grid_constant__ ArArgs<NV> args, long long numel, float scale,
+                      uint32_t epoch, unsigned long long timeout_ns, int gated, int unroll) {
+  const RankView& v = args.v[NV == 1 ? 0 : blockIdx.y];
+  const int rank = v.rank;
+  const int nb = gridDim.x, b = blockIdx.x, tid = threadIdx.x;
+  const long long npack = numel / 4;
+  const long long tail0 = npack * 4;
+  const long long Q = (npack + W - 1) / W;
+  const long long q = (Q + nb - 1) / nb;
+  float sq = 0.f;
+
+  if (comm_poisoned(v)) { poison_local(v, numel); return; }
+  if (!gated && !cross_barrier<W>(v, epoch, timeout_ns)) { poison_local(v, numel); return; }
+  const long long slo = min((long long)rank * Q, npack), shi = min(slo + Q, npack);
+  const long long lo = min(slo + (long long)b * q, shi), hi = min(lo + q, shi);
+  // loads in flight per thread = U x W x 16 B; B2_AR_UNROLL picks 0: the tuned default,
+  // 1: 16/W packs, 2: half the default
+  constexpr int kU0 = (W >= 8) ? 2 : 4, kU1 = (W >= 8) ? 2 : 16 / (W > 1 ? W : 2), kU2 = kU0 / 2;
+  if (unroll == 1) push_range<W, kU1>(v, lo, hi, scale, sq);
+  else if (unroll == 2) push_range<W, kU2>(v, lo, hi, scale, sq);
+  else push_range<W, kU0>(v, lo, hi, scale, sq);
   // tail (numel % 4): rank 0 owns it
   if (rank == 0 && b == 0 && tid < numel - tail0) {
     float acc = 0.f;
@@ -384,11 +442,14 @@ allreduce_push_kernel(const __grid_constant__ ArArgs<NV> args, long long numel, 
       const float t = __fmul_rn(Wire<false>::tail_load(v.stage[k] + tail0 * 4, tid), scale);
       acc = (k == 0) ? t : __fadd_rn(acc, t);
     }
+    sq = __fmaf_rn(acc, acc, sq);
 #pragma unroll
     for (int k = 0; k < W; ++k) reinterpret_cast<volatile float*>(v.stage[k] + tail0 * 4)[tid] = acc;
   }
+  if (v.sumsq) block_sumsq<W>(v, sq, true);
   __threadfence_system();  // this thread's remote stores are performed before the CTA signals
-  cross_barrier<W>(v, epoch + 1, timeout_ns);
+  if (!cross_barrier<W>(v, epoch + 1, timeout_ns)) { poison_local(v, numel); return; }
+  if (v.sumsq) fold_sumsq(v, 0, W);
 }
 
 // ---- host side ----------------------------------------------------------------------
@@ -459,14 +520,25 @@ extern "C" int b2_comm_create(int rank, int world, size_t staging_bytes, b2_comm
   c->rank = rank;
   c->world = world;
   c->half_bytes = (staging_bytes + 255) & ~(size_t)255;
-  c->max_blocks = (int)env_ll("B2_AR_BLOCKS", 96);
+  c->max_blocks = (int)env_ll("B2_AR_BLOCKS", 128);
   if (c->max_blocks < 1) c->max_blocks = 1;
   if (c->max_blocks > kArMaxBlocks) c->max_blocks = kArMaxBlocks;
-  c->timeout_ns = (unsigned long long)env_ll("B2_AR_TIMEOUT_MS", 30000) * 1000000ull;
+  c->unroll = (int)env_ll("B2_AR_UNROLL", 0);
+  // A peer that has not arrived after this long is treated as dead (NCCL-watchdog scale: a
+  // checkpoint save or an evaluation pass on one rank must not trip it).
+  c->timeout_ns = (unsigned long long)env_ll("B2_AR_TIMEOUT_MS", 600000) * 1000000ull;
   cudaError_t e = cudaGetDevice(&c->device);
   if (e == cudaSuccess) e = cudaMalloc((void**)&c->base[rank], kPadBytes + 2 * c->half_bytes);
   if (e == cudaSuccess) e = cudaMemset(c->base[rank], 0, kPadBytes);
+  // the status word's host mirror: mapped pinned memory, so b2_comm_poll is one host load
+  if (e == cudaSuccess) e = cudaHostAlloc((void**)&c->host_status, 64, cudaHostAllocMapped);
+  if (e == cudaSuccess) {
+    *c->host_status = 0;
+    e = cudaHostGetDevicePointer((void**)&c->host_status_dev, c->host_status, 0);
+  }
   if (e != cudaSuccess) {
+    if (c->base[rank]) cudaFree(c->base[rank]);
+    if (c->host_status) cudaFreeHost(c->host_status);
     delete c;
     return fail(B2_ERR_CUDA, "comm_create: %s", cudaGetErrorString(e));
   }
@@ -525,14 +597,14 @@ extern "C" int b2_allreduce(b2_comm* c, void* buf, int64_t numel, int wire_dtype
     const int a = algo == B2_ALGO_AUTO ? pick_algo(c->world, n * 4) : algo;
     ArArgs<1> args;
     RankView& v = args.v[0];
+    fill_view_common(c, v);
     v.buf = (float*)buf + off;
-    v.rank = c->rank;
-    for (int r = 0; r < B2_MAX_WORLD; ++r) {
-      char* base = c->base[r < c->world ? r : c->rank];
-      v.stage[r] = base + kPadBytes + (size_t)c->parity * c->half_bytes;
-      v.flags[r] = (uint32_t*)base;
+    for (int r = 0; r < B2_MAX_WORLD; ++r)
+      v.stage[r] = c->base[r < c->world ? r : c->rank] + kPadBytes + (size_t)c->parity * c->half_bytes;
+    if (c->sumsq) {
+      v.sumsq = (a == B2_ALGO_ONE_SHOT || c->world == 1) ? 1 : c->world;
+      c->sumsq_numel += n;
     }
-    v.status = (uint32_t*)(c->base[c->rank] + kStatusOff);
     KernelFn fn = pick_kernel<1>(c->world, bf16w, a);
     if (!fn) return fail(B2_ERR_INVALID, "allreduce: no kernel for world %d", c->world);
     const int nb = pick_blocks(n / epp, c->max_blocks);
@@ -649,14 +721,13 @@ extern "C" int b2_allreduce_registered(b2_comm* c, int reg_id, int64_t numel, fl
   if (numel == 0) return B2_OK;
   ArArgs<1> args;
   RankView& v = args.v[0];
+  fill_view_common(c, v);
   v.buf = (float*)reg.ptr[c->rank];
-  v.rank = c->rank;
-  for (int r = 0; r < B2_MAX_WORLD; ++r) {
-    const int k = r < c->world ? r : c->rank;
-    v.stage[r] = reg.ptr[k];
-    v.flags[r] = (uint32_t*)c->base[k];
+  for (int r = 0; r < B2_MAX_WORLD; ++r) v.stage[r] = reg.ptr[r < c->world ? r : c->rank];
+  if (c->sumsq) {
+    v.sumsq = c->world;
+    c->sumsq_numel += numel;
   }
-  v.status = (uint32_t*)(c->base[c->rank] + kStatusOff);
   static const bool pull = env_ll("B2_AR_ZERO_COPY_PULL", 0) != 0;  // A/B knob: two-shot pull variant
   KernelFn fn = pull ? pick_inplace_kernel<1>(c->world) : pick_push_kernel<1>(c->world);
   if (!fn) return fail(B2_ERR_INVALID, "allreduce_registered: no kernel for world %d", c->world);
@@ -672,7 +743,8 @@ extern "C" int b2_allreduce_registered(b2_comm* c, int reg_id, int64_t numel, fl
     void* gargs[] = {&args, &epoch, &to};
     B2_CUDA_CHECK(cudaLaunchKernel(gate, dim3(1), dim3(32), gargs, 0, (cudaStream_t)stream));
   }
-  void* kargs[] = {&args, &n_arg, &scale_arg, &epoch, &to, &gated};
+  int unroll = c->unroll;
+  void* kargs[] = {&args, &n_arg, &scale_arg, &epoch, &to, &gated, &unroll};  // the pull variant ignores the last
   B2_CUDA_CHECK(cudaLaunchKernel(fn, dim3(nb), dim3(kArThreads), kargs, 0, (cudaStream_t)stream));
   c->epoch += 3;  // gate, (barrier B of the pull variant,) final barrier
   return B2_OK;
@@ -700,13 +772,62 @@ extern "C" int b2_nvls_supported(int* supported_out) {
   return B2_OK;
 }
 
+static int timeout_error(const b2_comm* c) {
+  return b2::fail(B2_ERR_TIMEOUT,
+                  "all-reduce: a rank did not reach a cross-GPU barrier within %llu ms (B2_AR_TIMEOUT_MS); every "
+                  "bucket reduced since then was filled with NaN on every rank and this communicator is unusable",
+                  c->timeout_ns / 1000000ull);
+}
+
 extern "C" int b2_comm_status(b2_comm* c) {
   using namespace b2;
   B2_REQUIRE(c, "comm_status: null comm");
   uint32_t s = 0;
   B2_CUDA_CHECK(cudaMemcpy(&s, c->base[c->rank] + kStatusOff, 4, cudaMemcpyDeviceToHost));
-  if (s != 0) return fail(B2_ERR_TIMEOUT, "allreduce: a peer did not reach a barrier within %llu ms",
-                          c->timeout_ns / 1000000ull);
+  if (s != 0 || *(volatile uint32_t*)c->host_status != 0) return timeout_error(c);
+  return B2_OK;
+}
+
+extern "C" int b2_comm_poll(b2_comm* c) {
+  using namespace b2;
+  B2_REQUIRE(c, "comm_poll: null comm");
+  if (*(volatile uint32_t*)c->host_status != 0) return timeout_error(c);
+  return B2_OK;
+}
+
+extern "C" const void* b2_comm_status_word(b2_comm* c) { return c ? (const void*)c->host_status : nullptr; }
+
+namespace b2 {
+__global__ void sumsq_clip_kernel(double* acc, float max_norm, float* norm_out, float* coef_out) {
+  const float norm = (float)sqrt(*acc);
+  norm_out[0] = norm;
+  const float coef = max_norm / (norm + 1e-6f);  // torch: clamp(max_norm / (total_norm + 1e-6), max=1)
+  coef_out[0] = coef > 1.0f ? 1.0f : coef;
+  *acc = 0.0;
+}
+}  // namespace b2
+
+extern "C" int b2_comm_sumsq_enable(b2_comm* c, int on) {
+  using namespace b2;
+  B2_REQUIRE(c, "comm_sumsq_enable: null comm");
+  c->sumsq = on != 0;
+  c->sumsq_numel = 0;
+  B2_CUDA_CHECK(cudaMemset(c->base[c->rank] + kAccOff, 0, 8));
+  return B2_OK;
+}
+
+extern "C" int64_t b2_comm_sumsq_numel(b2_comm* c) { return c ? (int64_t)c->sumsq_numel : -1; }
+
+extern "C" int b2_comm_sumsq_clip(b2_comm* c, float max_norm, float* norm_out, float* coef_out,
+                                  b2_stream_t stream) {
+  using namespace b2;
+  B2_REQUIRE(c && norm_out && coef_out, "comm_sumsq_clip: null pointer");
+  B2_REQUIRE(max_norm > 0.f, "comm_sumsq_clip: max_norm must be positive");
+  if (!c->sumsq) return fail(B2_ERR_STATE, "comm_sumsq_clip: b2_comm_sumsq_enable has not been called");
+  sumsq_clip_kernel<<<1, 1, 0, (cudaStream_t)stream>>>((double*)(c->base[c->rank] + kAccOff), max_norm, norm_out,
+                                                       coef_out);
+  B2_CUDA_CHECK(cudaGetLastError());
+  c->sumsq_numel = 0;
   return B2_OK;
 }
 
@@ -719,6 +840,7 @@ extern "C" int b2_comm_destroy(b2_comm* c) {
     if (!c->base[r]) continue;
     if (r == c->rank) cudaFree(c->base[r]); else cudaIpcCloseMemHandle(c->base[r]);
   }
+  if (c->host_status) cudaFreeHost(c->host_status);
   delete c;
   return B2_OK;
 }
@@ -732,6 +854,12 @@ extern "C" size_t b2_allreduce_emulated_scratch_bytes(int world, int64_t numel) 
 extern "C" int b2_allreduce_emulated(void* const* bufs_host, int world, int64_t numel,
                                      int wire_dtype, float scale, int algo, void* staging,
                                      b2_stream_t stream) {
+  return b2_allreduce_emulated_sumsq(bufs_host, world, numel, wire_dtype, scale, algo, staging, nullptr, stream);
+}
+
+extern "C" int b2_allreduce_emulated_sumsq(void* const* bufs_host, int world, int64_t numel,
+                                           int wire_dtype, float scale, int algo, void* staging,
+                                           double* sumsq_out, b2_stream_t stream) {
   using namespace b2;
   B2_REQUIRE(bufs_host && staging, "allreduce_emulated: null pointer");
   B2_REQUIRE(world == 1 || world == 2 || world == 4 || world == 8, "allreduce_emulated: world %d", world);
@@ -762,6 +890,8 @@ extern "C" int b2_allreduce_emulated(void* const* bufs_host, int world, int64_t 
       v.flags[k] = (uint32_t*)base;
     }
     v.status = (uint32_t*)((char*)staging + (size_t)me * per_rank + kStatusOff);
+    v.host_status = v.status;  // no host mirror in the emulation
+    v.sumsq = !sumsq_out ? 0 : (algo == B2_ALGO_ONE_SHOT || world == 1) ? 1 : world;
   }
   KernelFn fn = (algo == B2_ALGO_TWO_SHOT_INPLACE) ? pick_inplace_kernel<B2_MAX_WORLD>(world)
               : (algo == B2_ALGO_PUSH_INPLACE)     ? pick_push_kernel<B2_MAX_WORLD>(world)
@@ -774,7 +904,12 @@ extern "C" int b2_allreduce_emulated(void* const* bufs_host, int world, int64_t 
   uint32_t epoch = 1;
   unsigned long long to = 5ull * 1000000000ull;
   int gated = 0;
-  void* kargs[] = {&args, &n_arg, &scale_arg, &epoch, &to, &gated};  // staging kernels ignore the extra slot
+  int unroll = 0;
+  void* kargs[] = {&args, &n_arg, &scale_arg, &epoch, &to, &gated, &unroll};  // staging kernels ignore the extra slots
   B2_CUDA_CHECK(cudaLaunchCooperativeKernel(fn, dim3(nb, world), dim3(kArThreads), kargs, 0, st));
+  if (sumsq_out)
+    for (int r = 0; r < world; ++r)
+      B2_CUDA_CHECK(cudaMemcpyAsync(sumsq_out + r, (char*)staging + (size_t)r * per_rank + kAccOff, 8,
+                                    cudaMemcpyDeviceToDevice, st));
   return B2_OK;
 }

@@ -30,6 +30,9 @@
 
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
+#include <utility>
+#include <vector>
 
 #include "allreduce_shared.cuh"
 
@@ -39,6 +42,8 @@ namespace b2 {
 // bump pointer inside it; used by b2_pool_alloc / b2_pool_free at the end of this file
 static b2_comm* g_pool_comm = nullptr;
 static size_t g_pool_next = 0;
+static std::vector<std::pair<size_t, size_t>> g_pool_free;  // (offset, bytes), sorted by offset, coalesced
+static std::mutex g_pool_mutex;
 
 struct Drv {
   CUresult (*memGetAllocationGranularity)(size_t*, const CUmemAllocationProp*, CUmemAllocationGranularity_flags);
@@ -149,7 +154,9 @@ allreduce_nvls_kernel(const __grid_constant__ NvlsArgs a, long long numel, float
   const long long Q = (npack + W - 1) / W;
   const long long q = (Q + nb - 1) / nb;
   constexpr int U = 4;
+  float sq = 0.f;
 
+  if (comm_poisoned(v)) { poison_local(v, numel); return; }
   // copy-in: this CTA stages its sub-range of every slice (the peer CTA with the same index
   // is the one whose switch read will touch it after the per-CTA barrier)
 #pragma unroll 1
@@ -170,7 +177,7 @@ allreduce_nvls_kernel(const __grid_constant__ NvlsArgs a, long long numel, float
   if (b == 0 && tid < numel - tail0)
     reinterpret_cast<float*>(a.uc + tail0 * 4)[tid] = __fmul_rn(buf[tail0 + tid], scale);
   __threadfence_system();
-  cross_barrier<W>(v, epoch, timeout_ns);
+  if (!cross_barrier<W>(v, epoch, timeout_ns)) { poison_local(v, numel); return; }
 
   // in-switch reduce + broadcast of my slice
   {
@@ -182,16 +189,26 @@ allreduce_nvls_kernel(const __grid_constant__ NvlsArgs a, long long numel, float
 #pragma unroll
       for (int u = 0; u < U; ++u) t[u] = multimem_ld_reduce_f32x4(a.mc + (i + u * kArThreads) * 16);
 #pragma unroll
-      for (int u = 0; u < U; ++u) multimem_st_f32x4(a.mc + (i + u * kArThreads) * 16, t[u]);
+      for (int u = 0; u < U; ++u) {
+        sq += sq4(t[u]);
+        multimem_st_f32x4(a.mc + (i + u * kArThreads) * 16, t[u]);
+      }
     }
-    for (; i < hi; i += kArThreads) multimem_st_f32x4(a.mc + i * 16, multimem_ld_reduce_f32x4(a.mc + i * 16));
+    for (; i < hi; i += kArThreads) {
+      const uint4 t = multimem_ld_reduce_f32x4(a.mc + i * 16);
+      sq += sq4(t);
+      multimem_st_f32x4(a.mc + i * 16, t);
+    }
     if (rank == 0 && b == 0 && tid < numel - tail0) {
       char* p = a.mc + tail0 * 4 + (size_t)tid * 4;
-      multimem_st_f32(p, multimem_ld_reduce_f32(p));
+      const float t = multimem_ld_reduce_f32(p);
+      sq = __fmaf_rn(t, t, sq);
+      multimem_st_f32(p, t);
     }
   }
+  if (v.sumsq) block_sumsq<W>(v, sq, true);
   __threadfence_system();
-  cross_barrier<W>(v, epoch + 1, timeout_ns);
+  if (!cross_barrier<W>(v, epoch + 1, timeout_ns)) { poison_local(v, numel); return; }
 
   // copy-out (system-scope loads: peers wrote this memory through the switch)
 #pragma unroll 1
@@ -210,6 +227,7 @@ allreduce_nvls_kernel(const __grid_constant__ NvlsArgs a, long long numel, float
   }
   if (b == 0 && tid < numel - tail0)
     buf[tail0 + tid] = Wire<false>::tail_load(a.uc + tail0 * 4, tid);
+  if (v.sumsq) fold_sumsq(v, 0, W);
 }
 
 }  // namespace b2
@@ -321,14 +339,13 @@ extern "C" int b2_allreduce_nvls(b2_comm* c, void* buf, int64_t numel, float sca
   for (long long off = 0; off < numel; off += cap) {
     const long long n = (numel - off < cap) ? (numel - off) : cap;
     NvlsArgs a;
+    fill_view_common(c, a.v);
     a.v.buf = (float*)buf + off;
-    a.v.rank = c->rank;
-    for (int r = 0; r < B2_MAX_WORLD; ++r) {
-      const int k = r < c->world ? r : c->rank;
-      a.v.stage[r] = nullptr;
-      a.v.flags[r] = (uint32_t*)c->base[k];
+    for (int r = 0; r < B2_MAX_WORLD; ++r) a.v.stage[r] = nullptr;
+    if (c->sumsq) {
+      a.v.sumsq = c->world;
+      c->sumsq_numel += n;
     }
-    a.v.status = (uint32_t*)(c->base[c->rank] + kStatusOff);
     a.uc = (char*)c->nvls.uc_va;
     a.mc = (char*)c->nvls.mc_va;
     const void* fn = c->world == 2 ? (const void*)allreduce_nvls_kernel<2>
@@ -355,8 +372,12 @@ int b2_nvls_release(b2_comm* c) {
   if (g_pool_comm == c && g_pool_next > n.stage_bytes) {
     // torch's caching allocator still owns segments inside the region (DDP buckets): unmapping
     // would leave it with dangling blocks. Keep the mappings; process teardown reclaims them.
-    // The communicator object itself is about to be deleted: detach it from the pool entry points.
+    // The communicator object itself is about to be deleted: detach it from the pool entry points
+    // and forget its bookkeeping (a later communicator starts from an empty region of its own).
+    std::lock_guard<std::mutex> lock(g_pool_mutex);
     g_pool_comm = nullptr;
+    g_pool_next = 0;
+    g_pool_free.clear();
     return B2_OK;
   }
   Drv* d;
@@ -376,6 +397,7 @@ int b2_nvls_release(b2_comm* c) {
   if (g_pool_comm == c) {
     g_pool_comm = nullptr;
     g_pool_next = 0;
+    g_pool_free.clear();
   }
   return B2_OK;
 }
@@ -391,10 +413,40 @@ int b2_nvls_release(b2_comm* c) {
 
 namespace b2 {
 
+__device__ __forceinline__ uint4 scale4(uint4 t, float scale) {
+  t.x = __float_as_uint(__fmul_rn(__uint_as_float(t.x), scale));
+  t.y = __float_as_uint(__fmul_rn(__uint_as_float(t.y), scale));
+  t.z = __float_as_uint(__fmul_rn(__uint_as_float(t.z), scale));
+  t.w = __float_as_uint(__fmul_rn(__uint_as_float(t.w), scale));
+  return t;
+}
+
+// U switch reads (16 bytes each) in flight per thread before the first multicast store.
+template <int U>
+__device__ __forceinline__ void nvls_range(char* mc, long long lo, long long hi, float scale, float& sq) {
+  long long i = lo + threadIdx.x;
+  for (; i + (U - 1) * kArThreads < hi; i += U * kArThreads) {
+    uint4 t[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) t[u] = multimem_ld_reduce_f32x4(mc + (i + u * kArThreads) * 16);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      t[u] = scale4(t[u], scale);
+      sq += sq4(t[u]);
+      multimem_st_f32x4(mc + (i + u * kArThreads) * 16, t[u]);
+    }
+  }
+  for (; i < hi; i += kArThreads) {
+    const uint4 t = scale4(multimem_ld_reduce_f32x4(mc + i * 16), scale);
+    sq += sq4(t);
+    multimem_st_f32x4(mc + i * 16, t);
+  }
+}
+
 template <int W>
 __global__ void __launch_bounds__(kArThreads, 1)
 allreduce_nvls_inplace_kernel(const __grid_constant__ NvlsArgs a, long long numel, float scale,
-                              uint32_t epoch, unsigned long long timeout_ns, int gated) {
+                              uint32_t epoch, unsigned long long timeout_ns, int gated, int unroll) {
   const RankView& v = a.v;
   const int rank = v.rank;
   const int nb = gridDim.x, b = blockIdx.x, tid = threadIdx.x;
@@ -402,38 +454,25 @@ allreduce_nvls_inplace_kernel(const __grid_constant__ NvlsArgs a, long long nume
   const long long tail0 = npack * 4;
   const long long Q = (npack + W - 1) / W;
   const long long q = (Q + nb - 1) / nb;
-  constexpr int U = 4;
-  if (!gated) cross_barrier<W>(v, epoch, timeout_ns);
+  float sq = 0.f;
+  if (comm_poisoned(v)) { poison_local(v, numel); return; }
+  if (!gated && !cross_barrier<W>(v, epoch, timeout_ns)) { poison_local(v, numel); return; }
   const long long slo = min((long long)rank * Q, npack), shi = min(slo + Q, npack);
   const long long lo = min(slo + (long long)b * q, shi), hi = min(lo + q, shi);
-  long long i = lo + tid;
-  for (; i + (U - 1) * kArThreads < hi; i += U * kArThreads) {
-    uint4 t[U];
-#pragma unroll
-    for (int u = 0; u < U; ++u) t[u] = multimem_ld_reduce_f32x4(a.mc + (i + u * kArThreads) * 16);
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      t[u].x = __float_as_uint(__fmul_rn(__uint_as_float(t[u].x), scale));
-      t[u].y = __float_as_uint(__fmul_rn(__uint_as_float(t[u].y), scale));
-      t[u].z = __float_as_uint(__fmul_rn(__uint_as_float(t[u].z), scale));
-      t[u].w = __float_as_uint(__fmul_rn(__uint_as_float(t[u].w), scale));
-      multimem_st_f32x4(a.mc + (i + u * kArThreads) * 16, t[u]);
-    }
-  }
-  for (; i < hi; i += kArThreads) {
-    uint4 t = multimem_ld_reduce_f32x4(a.mc + i * 16);
-    t.x = __float_as_uint(__fmul_rn(__uint_as_float(t.x), scale));
-    t.y = __float_as_uint(__fmul_rn(__uint_as_float(t.y), scale));
-    t.z = __float_as_uint(__fmul_rn(__uint_as_float(t.z), scale));
-    t.w = __float_as_uint(__fmul_rn(__uint_as_float(t.w), scale));
-    multimem_st_f32x4(a.mc + i * 16, t);
-  }
+  // B2_AR_UNROLL: 0 = 4 (default), 1 = 8, 2 = 2 switch reads in flight per thread
+  if (unroll == 1) nvls_range<8>(a.mc, lo, hi, scale, sq);
+  else if (unroll == 2) nvls_range<2>(a.mc, lo, hi, scale, sq);
+  else nvls_range<4>(a.mc, lo, hi, scale, sq);
   if (rank == 0 && b == 0 && tid < numel - tail0) {
     char* p = a.mc + tail0 * 4 + (size_t)tid * 4;
-    multimem_st_f32(p, __fmul_rn(multimem_ld_reduce_f32(p), scale));
+    const float t = __fmul_rn(multimem_ld_reduce_f32(p), scale);
+    sq = __fmaf_rn(t, t, sq);
+    multimem_st_f32(p, t);
   }
+  if (v.sumsq) block_sumsq<W>(v, sq, true);
   __threadfence_system();
-  cross_barrier<W>(v, epoch + 1, timeout_ns);
+  if (!cross_barrier<W>(v, epoch + 1, timeout_ns)) { poison_local(v, numel); return; }
+  if (v.sumsq) fold_sumsq(v, 0, W);
 }
 
 }  // namespace b2
@@ -441,24 +480,59 @@ allreduce_nvls_inplace_kernel(const __grid_constant__ NvlsArgs a, long long nume
 // torch.cuda.memory.CUDAPluggableAllocator entry points (alloc_fn / free_fn signatures): a bump
 // allocator over the multicast-bound region of the communicator attached with
 // b2_nvls_pool_attach. torch's caching allocator asks for whole segments and sub-allocates.
+// Freed segments go to a sorted, coalescing free list and are handed out again first-fit, so a
+// re-wrapped DDP model (a second Reducer, a second set of buckets) reuses the region instead of
+// leaking it; segments are 2 MiB-granular like the caching allocator's own.
 extern "C" void* b2_pool_alloc(ssize_t size, int device, void* stream) {
   (void)stream;
+  std::lock_guard<std::mutex> lock(b2::g_pool_mutex);
   b2_comm* c = b2::g_pool_comm;
   if (!c || !c->nvls.ready || device != c->device || size <= 0) return nullptr;
   const size_t align = 2ull << 20;
+  const size_t need = ((size_t)size + align - 1) / align * align;
+  for (size_t i = 0; i < b2::g_pool_free.size(); ++i) {
+    auto& f = b2::g_pool_free[i];
+    if (f.second >= need) {
+      const size_t off = f.first;
+      if (f.second == need) b2::g_pool_free.erase(b2::g_pool_free.begin() + i);
+      else { f.first += need; f.second -= need; }
+      return (void*)(c->nvls.uc_va + off);
+    }
+  }
   if (b2::g_pool_next < c->nvls.stage_bytes) b2::g_pool_next = c->nvls.stage_bytes;
   const size_t off = (b2::g_pool_next + align - 1) / align * align;
-  if (off + (size_t)size > c->nvls.bytes) return nullptr;  // torch reports out-of-memory
-  b2::g_pool_next = off + (size_t)size;
+  if (off + need > c->nvls.bytes) return nullptr;  // torch reports out-of-memory
+  b2::g_pool_next = off + need;
   return (void*)(c->nvls.uc_va + off);
 }
 
 extern "C" void b2_pool_free(void* ptr, ssize_t size, int device, void* stream) {
   (void)device; (void)stream;
+  std::lock_guard<std::mutex> lock(b2::g_pool_mutex);
   b2_comm* c = b2::g_pool_comm;
-  if (!c || !ptr) return;
-  const size_t off = (size_t)((CUdeviceptr)(uintptr_t)ptr - c->nvls.uc_va);
-  if (off + (size_t)size == b2::g_pool_next) b2::g_pool_next = off;  // last block: reuse; others stay reserved
+  if (!c || !ptr || size <= 0) return;
+  const size_t align = 2ull << 20;
+  const CUdeviceptr addr = (CUdeviceptr)(uintptr_t)ptr;
+  // a segment of an earlier communicator's region (torch releases a MemPool lazily): not ours
+  if (addr < c->nvls.uc_va || addr >= c->nvls.uc_va + c->nvls.bytes) return;
+  const size_t off = (size_t)(addr - c->nvls.uc_va);
+  const size_t len = ((size_t)size + align - 1) / align * align;
+  auto& fl = b2::g_pool_free;
+  size_t i = 0;
+  while (i < fl.size() && fl[i].first < off) ++i;
+  fl.insert(fl.begin() + i, std::make_pair(off, len));
+  if (i + 1 < fl.size() && fl[i].first + fl[i].second == fl[i + 1].first) {  // merge with the next block
+    fl[i].second += fl[i + 1].second;
+    fl.erase(fl.begin() + i + 1);
+  }
+  if (i > 0 && fl[i - 1].first + fl[i - 1].second == fl[i].first) {          // and with the previous one
+    fl[i - 1].second += fl[i].second;
+    fl.erase(fl.begin() + i);
+  }
+  if (!fl.empty() && fl.back().first + fl.back().second == b2::g_pool_next) {  // top of the bump area
+    b2::g_pool_next = fl.back().first;
+    fl.pop_back();
+  }
 }
 
 extern "C" int b2_nvls_pool_attach(b2_comm* c) {
@@ -490,14 +564,13 @@ extern "C" int b2_allreduce_nvls_inplace(b2_comm* c, uint64_t offset_bytes, int6
              (unsigned long long)offset_bytes, (long long)numel, c->nvls.bytes);
   if (numel == 0) return B2_OK;
   NvlsArgs a;
+  fill_view_common(c, a.v);
   a.v.buf = (float*)(c->nvls.uc_va + offset_bytes);
-  a.v.rank = c->rank;
-  for (int r = 0; r < B2_MAX_WORLD; ++r) {
-    const int k = r < c->world ? r : c->rank;
-    a.v.stage[r] = nullptr;
-    a.v.flags[r] = (uint32_t*)c->base[k];
+  for (int r = 0; r < B2_MAX_WORLD; ++r) a.v.stage[r] = nullptr;
+  if (c->sumsq) {
+    a.v.sumsq = c->world;
+    c->sumsq_numel += numel;
   }
-  a.v.status = (uint32_t*)(c->base[c->rank] + kStatusOff);
   a.uc = (char*)(c->nvls.uc_va + offset_bytes);
   a.mc = (char*)(c->nvls.mc_va + offset_bytes);
   uint32_t epoch = c->epoch;
@@ -516,7 +589,8 @@ extern "C" int b2_allreduce_nvls_inplace(b2_comm* c, uint64_t offset_bytes, int6
   const int nb = pick_blocks(numel / 4 / c->world, c->max_blocks);
   long long n_arg = numel;
   float scale_arg = scale;
-  void* kargs[] = {&a, &n_arg, &scale_arg, &epoch, &to, &gated};
+  int unroll = c->unroll;
+  void* kargs[] = {&a, &n_arg, &scale_arg, &epoch, &to, &gated, &unroll};
   B2_CUDA_CHECK(cudaLaunchKernel(fn, dim3(nb), dim3(kArThreads), kargs, 0, (cudaStream_t)stream));
   c->epoch += 2;
   return B2_OK;

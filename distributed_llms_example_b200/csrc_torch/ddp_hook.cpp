@@ -40,13 +40,16 @@ struct Entry {
 struct Shared {
   std::vector<Entry> table;
   uint64_t fast_calls = 0, slow_calls = 0;
+  bool closed = false;  // set by P2PComm.close() through Handle::close(): the communicator is gone
 };
 
 class B2CommHook : public c10d::CommHookInterface {
  public:
   B2CommHook(py::object hook, py::object state, uintptr_t ctx, uintptr_t fn_registered, uintptr_t fn_nvls,
-             double scale, int device, int64_t side_stream_id, std::shared_ptr<Shared> shared)
+             double scale, int device, int64_t side_stream_id, uintptr_t status_word,
+             std::shared_ptr<Shared> shared)
       : hook_(std::move(hook)), state_(std::move(state)), ctx_(reinterpret_cast<void*>(ctx)),
+        status_(reinterpret_cast<const volatile uint32_t*>(status_word)),
         fn_registered_(reinterpret_cast<RegisteredFn>(fn_registered)), fn_nvls_(reinterpret_cast<NvlsFn>(fn_nvls)),
         scale_(static_cast<float>(scale)), device_(device),
         side_(c10::cuda::CUDAStream::unpack3(side_stream_id, static_cast<c10::DeviceIndex>(device),
@@ -62,6 +65,12 @@ class B2CommHook : public c10d::CommHookInterface {
   c10::intrusive_ptr<c10::ivalue::Future> runHook(c10d::GradBucket& bucket) override {
     const size_t idx = bucket.getIndex();
     at::Tensor& buf = bucket.getBufferRef();
+    TORCH_CHECK(!shared_->closed, "b200 DDP hook: its communicator has been closed (P2PComm.close()); "
+                "register a new hook before running backward on this DDP module");
+    // one host load of the mapped status word (include/b2ddp.h, b2_comm_status_word): a peer that
+    // missed a barrier poisoned the buckets with NaN; stop here, on every rank, instead of training on
+    TORCH_CHECK(status_ == nullptr || *status_ == 0u, "libb2ddp error -4: a rank did not reach a cross-GPU "
+                "barrier in time (B2_AR_TIMEOUT_MS); gradients since then are NaN-filled on every rank");
     if (idx < shared_->table.size()) {
       const Entry& e = shared_->table[idx];
       if (e.kind >= 0 && e.ptr == reinterpret_cast<uintptr_t>(buf.data_ptr()) && e.numel == buf.numel()) {
@@ -98,6 +107,7 @@ class B2CommHook : public c10d::CommHookInterface {
  private:
   py::object hook_, state_;
   void* ctx_;
+  const volatile uint32_t* status_;
   RegisteredFn fn_registered_;
   NvlsFn fn_nvls_;
   float scale_;
@@ -114,17 +124,22 @@ struct Handle {
     if (shared->table.size() <= index) shared->table.resize(index + 1);
     shared->table[index] = Entry{ptr, numel, kind, arg};
   }
+  void close() {
+    shared->closed = true;
+    shared->table.clear();
+  }
   uint64_t fast_calls() const { return shared->fast_calls; }
   uint64_t slow_calls() const { return shared->slow_calls; }
 };
 
 std::shared_ptr<Handle> attach(py::object reducer, py::object hook, py::object state, uintptr_t ctx,
                                uintptr_t fn_registered, uintptr_t fn_nvls, double scale, int device,
-                               int64_t side_stream_id) {
+                               int64_t side_stream_id, uintptr_t status_word) {
   auto r = reducer.cast<std::shared_ptr<c10d::Reducer>>();
   auto handle = std::make_shared<Handle>();
   r->register_comm_hook(std::make_unique<B2CommHook>(std::move(hook), std::move(state), ctx, fn_registered,
-                                                      fn_nvls, scale, device, side_stream_id, handle->shared));
+                                                      fn_nvls, scale, device, side_stream_id, status_word,
+                                                      handle->shared));
   return handle;
 }
 
@@ -133,6 +148,7 @@ std::shared_ptr<Handle> attach(py::object reducer, py::object hook, py::object s
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   py::class_<Handle, std::shared_ptr<Handle>>(m, "Handle")
       .def("set_entry", &Handle::set_entry)
+      .def("close", &Handle::close)
       .def_property_readonly("fast_calls", &Handle::fast_calls)
       .def_property_readonly("slow_calls", &Handle::slow_calls);
   m.def("attach", &attach, "Register the C++ comm hook on a c10d::Reducer");

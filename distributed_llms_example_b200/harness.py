@@ -70,7 +70,9 @@ class StepHarness:
         if cfg.impl == "b200":
             if self.device.type != "cuda":
                 raise RuntimeError("impl='b200' has no CPU path")
-            patch.apply(ddp=False)
+            # the same attach path an unmodified script gets from launch.py: CrossEntropyLoss,
+            # torch.optim.AdamW, clip_grad_norm_ and DistributedDataParallel.__init__ are rebound
+            patch.apply(comm_kwargs={"wire": cfg.wire})
         elif cfg.impl == "stock":
             patch.remove()
         else:
@@ -97,9 +99,8 @@ class StepHarness:
         else:
             raise ValueError(cfg.semantics)
         if cfg.impl == "b200":
-            from .optim import AdamW
-
-            self.optimizer = AdamW(groups, lr=cfg.lr, **kw)
+            # what the scripts' ``from torch.optim import AdamW`` resolves to after patch.apply()
+            self.optimizer = torch.optim.AdamW(groups, lr=cfg.lr, **kw)
         else:
             fused = cfg.fused_adamw
             if fused is None:
@@ -123,9 +124,8 @@ class StepHarness:
                 extra = {} if cfg.bucket_cap_mb is None else {"bucket_cap_mb": cfg.bucket_cap_mb}
                 self.ddp = DDP(self.model, device_ids=ids, find_unused_parameters=False, **extra)
                 if cfg.impl == "b200":
-                    from .comm import register_p2p_comm_hook
-
-                    self.hook_state = register_p2p_comm_hook(self.ddp, wire=cfg.wire)
+                    # registered by the patched DDP.__init__ (patch.patch_ddp), not by hand
+                    self.hook_state = self.ddp._b200_hook_state
         self.collate = Seq2SeqCollator(pad_to_multiple_of=8 if cfg.label_mode == "MASK" else None,
                                        pin_memory=self.device.type == "cuda")
         self.steps_done = 0
@@ -181,10 +181,10 @@ class StepHarness:
                     dist.all_reduce(p.grad.data, op=dist.ReduceOp.SUM)
                     p.grad.data /= size
         if cfg.semantics == "trainer" and cfg.max_grad_norm:
-            if cfg.impl == "b200":
-                self.optimizer.clip_grad_norm_(cfg.max_grad_norm)  # folded into the AdamW launch
-            else:
-                torch.nn.utils.clip_grad_norm_(self.model.parameters(), cfg.max_grad_norm)
+            # what HF Trainer calls (trainer.py:1753-1757); with impl="b200" the name is rebound by
+            # patch.patch_clip_grad_norm and routed to AdamW.clip_grad_norm_ (norm from the
+            # all-reduce's fold or one read-only pass; the multiply happens inside the AdamW launch)
+            torch.nn.utils.clip_grad_norm_(self.model.parameters(), cfg.max_grad_norm)
         self.optimizer.step()
         self.scheduler.step()
         self.optimizer.zero_grad()

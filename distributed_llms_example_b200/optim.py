@@ -15,6 +15,7 @@ scripts' schedule), state_dict layout matches torch's (``step`` fp32 CPU scalar 
 from __future__ import annotations
 
 import ctypes as C
+import sys
 import weakref
 from typing import Any, Callable, Iterable, Optional
 
@@ -87,7 +88,25 @@ class AdamW(Optimizer):
         #: launching stream tightly around the kernel launch (bench.py's roofline timing).
         self.kernel_events: Optional[list] = None
         self._norm_ws: Optional[torch.Tensor] = None
+        #: where the last clip_grad_norm_ got its norm: "allreduce" (folded into the gradient
+        #: all-reduce, no extra pass) or "kernel" (grad_sumsq_kernel, one read of the gradients)
+        self.norm_source: Optional[str] = None
         _LIVE.add(self)
+
+    _UNSUPPORTED = ("amsgrad", "maximize", "capturable", "differentiable")
+
+    def _validate_groups(self) -> None:
+        """The constructor's contract also holds for param_groups that arrive through
+        load_state_dict / unpickling: a checkpoint written by torch.optim.AdamW(amsgrad=True) must not
+        resume with different semantics in silence."""
+        for i, group in enumerate(self.param_groups):
+            for name in self._UNSUPPORTED:
+                if group.get(name, False):
+                    raise NotImplementedError(
+                        f"b200 AdamW: param group {i} has {name}=True, which this optimizer does not implement "
+                        "(the checkpoint was written by an optimizer with other semantics)")
+            if isinstance(group.get("lr"), torch.Tensor):
+                raise NotImplementedError("b200 AdamW: tensor lr is not supported (host scalar lr only)")
 
     def __setstate__(self, state: dict[str, Any]) -> None:
         super().__setstate__(state)
@@ -96,10 +115,12 @@ class AdamW(Optimizer):
         self.__dict__.setdefault("grad_scale", None)
         self.__dict__.setdefault("kernel_events", None)
         self.__dict__.setdefault("_norm_ws", None)
+        self.__dict__.setdefault("norm_source", None)
         for group in self.param_groups:
             group.setdefault("amsgrad", False)
             group.setdefault("maximize", False)
             group.setdefault("decoupled_weight_decay", True)
+        self._validate_groups()
 
     # -- plan: everything about a step that does not change from one step to the next -----
     def add_param_group(self, param_group: dict[str, Any]) -> None:
@@ -108,7 +129,14 @@ class AdamW(Optimizer):
         self._all_params = None
 
     def load_state_dict(self, state_dict: dict[str, Any]) -> None:
+        for i, group in enumerate(state_dict.get("param_groups", [])):  # refuse BEFORE mutating self
+            for name in self._UNSUPPORTED:
+                if group.get(name, False):
+                    raise NotImplementedError(
+                        f"b200 AdamW: the state dict's param group {i} has {name}=True, which this optimizer "
+                        "does not implement")
         super().load_state_dict(state_dict)
+        self._validate_groups()
         self._plan = None
         self._all_params = None
 
@@ -246,6 +274,27 @@ class AdamW(Optimizer):
         if plan is None:
             return torch.zeros((), dtype=torch.float32)
         device = plan.device
+        # At world size > 1 the all-reduce has already summed the squares of every reduced gradient
+        # element while it held them in registers: if its count covers exactly
+        # this optimizer's gradients, the norm costs a one-thread kernel and no read of the gradients.
+        comm_mod = sys.modules.get(__package__ + ".comm")
+        if comm_mod is not None:
+            total = int(plan.host["numel"].sum())
+            for comm in comm_mod.live_comms():
+                if comm.world < 2 or comm.device != device:
+                    continue
+                if not comm.sumsq_enabled:
+                    comm.enable_sumsq(True)  # from the next step on (every rank gets here together)
+                    continue
+                if comm.sumsq_numel() == total:
+                    out = torch.empty(2, dtype=torch.float32, device=device)  # [norm, coef]
+                    with torch.cuda.device(device):
+                        comm.sumsq_clip_(float(max_norm), out)
+                    self.grad_scale = out[1:2]
+                    self.norm_source = "allreduce"
+                    return out[0]
+                comm.enable_sumsq(True)  # count does not match these gradients: reset, use the kernel below
+        self.norm_source = "kernel"
         with torch.cuda.device(device):
             if plan.dirty:
                 self._upload_table(plan)
@@ -277,6 +326,9 @@ class AdamW(Optimizer):
         plan = self._refresh()
         if plan is None:
             return loss
+        comm_mod = sys.modules.get(__package__ + ".comm")
+        if comm_mod is not None:
+            comm_mod.poll_all()  # never apply gradients a timed-out all-reduce filled with NaN
         n = plan.n
         # state["step"] += 1 for every live param, in one call; python mirror for the scalars
         plan.step_flat.add_(1)

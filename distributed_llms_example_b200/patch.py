@@ -45,31 +45,53 @@ def patch_adamw() -> None:
     torch.optim.AdamW = AdamW
 
 
+_ddp_comm_kwargs: dict[str, Any] = {}
+
+
+def _wants_hook(module, kwargs) -> bool:
+    """A DDP module gets the peer-memory hook when its parameters live on a CUDA device and its
+    process group has more than one rank (CPU / gloo modules and world size 1 are left alone)."""
+    import torch.distributed as dist
+
+    first = next(module.parameters(), None)
+    return (first is not None and first.is_cuda and dist.is_initialized()
+            and dist.get_world_size(kwargs.get("process_group")) > 1)
+
+
 def patch_ddp(**comm_kwargs) -> None:
     """Every DistributedDataParallel built afterwards on a CUDA device with world size > 1 gets
-    the peer-memory all-reduce hook."""
+    the peer-memory all-reduce hook (``comm_kwargs`` go to ``register_p2p_comm_hook``; calling
+    this again only replaces them). Two constructor defaults change where the caller left them
+    unset - none of the reference scripts sets either:
+
+      * ``gradient_as_bucket_view=True``: ``p.grad`` aliases the Reducer's bucket, so the
+        bucket -> ``p.grad`` copy-out after every all-reduce (one kernel per parameter, 2 x the
+        gradient bytes) disappears and the optimizer's gradient addresses stay the same from
+        step to step (``B2_DDP_BUCKET_VIEW=0`` keeps torch's default);
+      * ``bucket_cap_mb`` from ``B2_DDP_BUCKET_MB`` when that is set (fewer, larger buckets).
+    """
     from torch.nn.parallel import DistributedDataParallel as DDP
 
+    _ddp_comm_kwargs.clear()
+    _ddp_comm_kwargs.update(comm_kwargs)
     if "ddp_init" in _saved:
         return
     orig = DDP.__init__
     _saved["ddp_init"] = orig
 
     def __init__(self, module, *args, **kwargs):
-        # Optional: fewer, larger buckets mean fewer Python hook calls on the autograd thread
-        # (each costs ~25 us against ~10 us for NCCL's C++ path). Off unless B2_DDP_BUCKET_MB is set,
-        # so the script's own (default) bucketing is what runs.
-        cap = os.environ.get("B2_DDP_BUCKET_MB")
-        if cap and "bucket_cap_mb" not in kwargs:
-            kwargs["bucket_cap_mb"] = float(cap)
+        ours = _wants_hook(module, kwargs)
+        if ours:
+            cap = os.environ.get("B2_DDP_BUCKET_MB")
+            if cap and "bucket_cap_mb" not in kwargs:
+                kwargs["bucket_cap_mb"] = float(cap)
+            if "gradient_as_bucket_view" not in kwargs and os.environ.get("B2_DDP_BUCKET_VIEW", "1") != "0":
+                kwargs["gradient_as_bucket_view"] = True
         orig(self, module, *args, **kwargs)
-        import torch.distributed as dist
+        if ours:
+            from . import comm
 
-        first = next(module.parameters(), None)
-        if first is not None and first.is_cuda and dist.get_world_size(self.process_group) > 1:
-            from .comm import register_p2p_comm_hook
-
-            self._b200_hook_state = register_p2p_comm_hook(self, **comm_kwargs)
+            self._b200_hook_state = comm.register_p2p_comm_hook(self, **_ddp_comm_kwargs)
 
     DDP.__init__ = __init__
 
@@ -99,13 +121,14 @@ def patch_clip_grad_norm() -> None:
     U.clip_grad_norm_ = clip_grad_norm_
 
 
-def apply(cross_entropy: bool = True, adamw: bool = True, ddp: bool = True, fold_clip: bool = True) -> None:
+def apply(cross_entropy: bool = True, adamw: bool = True, ddp: bool = True, fold_clip: bool = True,
+          comm_kwargs: dict | None = None) -> None:
     if cross_entropy:
         patch_cross_entropy()
     if adamw:
         patch_adamw()
     if ddp:
-        patch_ddp()
+        patch_ddp(**(comm_kwargs or {}))
     if fold_clip:
         patch_clip_grad_norm()
 

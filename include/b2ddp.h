@@ -249,8 +249,35 @@ void* b2_pool_alloc(ssize_t size, int device, void* stream);
 void b2_pool_free(void* ptr, ssize_t size, int device, void* stream);
 int b2_allreduce_nvls_inplace(b2_comm* c, uint64_t offset_bytes, int64_t numel, float scale,
                               b2_stream_t stream);
-/* 0, or B2_ERR_TIMEOUT once a kernel gave up waiting for a peer (sticky). */
+/* A peer that does not reach a cross-GPU barrier within B2_AR_TIMEOUT_MS (default 600 000 ms,
+ * the scale of NCCL's watchdog) is an error, never silently wrong gradients: the rank that gave
+ * up raises a sticky status word on EVERY rank, and from then on every all-reduce of this
+ * communicator on every rank fills the bucket it was given with NaN instead of reducing it
+ * (NCCL would block or abort where the reference calls it: train-task.py:68, the Reducer's
+ * all-reduce behind train-accelerator.py:222 / train-torchrun.py:140).
+ * b2_comm_status: synchronising check (copies the device word). b2_comm_poll: the same answer
+ * from one plain host load of a mapped pinned word the kernels mirror the status into - cheap
+ * enough to call every step (the Python adapters do, in the DDP hook, average_gradients and
+ * AdamW.step). b2_comm_status_word: host address of that word (non-zero = timed out), for
+ * callers that poll from their own C++ (csrc_torch/ddp_hook.cpp). */
 int b2_comm_status(b2_comm* c);
+int b2_comm_poll(b2_comm* c);
+const void* b2_comm_status_word(b2_comm* c);
+/* Sum of squares folded into the all-reduce: replaces the separate read of
+ * every gradient that torch.nn.utils.clip_grad_norm_ makes between sync and step in HF Trainer
+ * (SP/transformers/trainer.py:1753-1757, max_grad_norm=1.0; train-torchrun.py:115-128,140). Once
+ * enabled, every all-reduce of this communicator (staging, registered, NVLS) also accumulates
+ * sum(x*x) over the reduced values it produced - the slice owner has them in registers - into a
+ * double kept in the communicator: per-CTA partials in a fixed order, exchanged with the data,
+ * so the total is bit-identical on every rank and run to run. b2_comm_sumsq_numel: elements
+ * folded since the last b2_comm_sumsq_clip / b2_comm_sumsq_enable (host-side count; the caller
+ * checks it covers exactly the gradients it is about to clip). b2_comm_sumsq_clip: one-thread
+ * kernel on `stream` (which must be ordered after the all-reduces): norm_out[0] = sqrt(total),
+ * coef_out[0] = min(1, max_norm / (norm + 1e-6)), total <- 0. */
+int b2_comm_sumsq_enable(b2_comm* c, int on);
+int64_t b2_comm_sumsq_numel(b2_comm* c);
+int b2_comm_sumsq_clip(b2_comm* c, float max_norm, float* norm_out, float* coef_out,
+                       b2_stream_t stream);
 int b2_comm_destroy(b2_comm* c);
 
 /* Test hook for machines with fewer GPUs than ranks: the same device code run as
@@ -262,6 +289,11 @@ size_t b2_allreduce_emulated_scratch_bytes(int world, int64_t numel);
 int b2_allreduce_emulated(void* const* bufs_host, int world, int64_t numel,
                           int wire_dtype, float scale, int algo, void* staging,
                           b2_stream_t stream);
+/* Same, with the sum-of-squares fold switched on: sumsq_out (device, double[world]) receives
+ * each virtual rank's total (all equal). */
+int b2_allreduce_emulated_sumsq(void* const* bufs_host, int world, int64_t numel,
+                                int wire_dtype, float scale, int algo, void* staging,
+                                double* sumsq_out, b2_stream_t stream);
 
 #ifdef __cplusplus
 }

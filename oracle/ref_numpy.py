@@ -139,6 +139,13 @@ def allreduce_mean_bf16_wire(bufs: list[np.ndarray], scale: float | None = None)
     return _round_bf16(acc)
 
 
+def grad_sumsq(x: np.ndarray) -> float:
+    """sum(x*x) of float32 values, accumulated in float64: what the norm of
+    torch.nn.utils.clip_grad_norm_ is the square root of (SP/transformers/trainer.py:1753-1757)."""
+    x = np.asarray(x, dtype=np.float64).reshape(-1)
+    return float(np.dot(x, x))
+
+
 def clip_coef(total_norm: float, max_norm: float) -> float:
     """torch.nn.utils.clip_grad_norm_ coefficient: clamp(max_norm / (norm + 1e-6), max=1)
     (HF Trainer default max_grad_norm=1.0, SP/transformers/trainer.py:1753-1757)."""

@@ -85,6 +85,49 @@ def test_emulated_large_bucket_25mib():
             np.testing.assert_array_equal(out[r], ref)
 
 
+def emulated_sumsq(bufs_np, wire, algo):
+    L, lib = _L()
+    w, n = len(bufs_np), bufs_np[0].size
+    bufs = [torch.from_numpy(b.copy()).to(DEV) for b in bufs_np]
+    nbytes = lib.b2_allreduce_emulated_scratch_bytes(w, n)
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=DEV)
+    sumsq = torch.full((w,), -1.0, dtype=torch.float64, device=DEV)
+    ptrs = (ctypes.c_void_p * w)(*[b.data_ptr() for b in bufs])
+    L.check(lib.b2_allreduce_emulated_sumsq(ptrs, w, n, wire, 1.0 / w, algo, scratch.data_ptr(), sumsq.data_ptr(),
+                                            torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    return [b.cpu().numpy() for b in bufs], sumsq.cpu().numpy()
+
+
+@pytest.mark.parametrize("algo", [1, 2, 3, 4])
+@pytest.mark.parametrize("w", [1, 2, 4, 8])
+@pytest.mark.parametrize("n", [3, 4, 1023, 8 * 512 * 4 * 3 + 5, (1 << 20) + 1])
+def test_emulated_sum_of_squares_fold(w, n, algo):
+    """the all-reduce also returns sum(x*x) of the reduced values (what the gradient
+    clip needs), identical on every rank, bit-identical run to run, 2e-6 from the float64 oracle;
+    the reduced values themselves stay bit-exact."""
+    bufs = allreduce_inputs(w, n, 1100 + n % 97)
+    ref = O.allreduce_mean(bufs)
+    out, sq = emulated_sumsq(bufs, 0, algo)
+    for r in range(w):
+        np.testing.assert_array_equal(out[r], ref, err_msg=f"rank {r}")
+    want = O.grad_sumsq(ref)
+    assert np.all(sq == sq[0]), sq                      # every rank holds the same total
+    assert abs(sq[0] - want) <= 2e-6 * want, (sq[0], want)
+    _, sq2 = emulated_sumsq(bufs, 0, algo)
+    assert np.array_equal(sq, sq2)                      # deterministic
+
+
+def test_emulated_sum_of_squares_bf16_wire_counts_the_rounded_values():
+    bufs = allreduce_inputs(4, 70001, 5)
+    ref = O.allreduce_mean_bf16_wire(bufs)
+    for algo in (1, 2):
+        out, sq = emulated_sumsq(bufs, 1, algo)
+        np.testing.assert_array_equal(out[0], ref)
+        want = O.grad_sumsq(ref)
+        assert np.all(sq == sq[0]) and abs(sq[0] - want) <= 2e-6 * want
+
+
 def test_comm_world_1_scales_in_place():
     from distributed_llms_example_b200.comm import P2PComm
 
@@ -195,6 +238,39 @@ def _worker(rank, world, port, q):
             results[("average_gradients", rep)] = bool(ok)
         comm.check()
 
+        # sum of squares folded into the all-reduce (8f row 1) on the real paths: identical on every
+        # rank, 2e-6 from the float64 oracle, consumed and reset by sumsq_clip_
+        comm.enable_sumsq(True)
+        n = (5 << 20) // 4 + 3
+        xr = torch.empty(n, device="cuda")
+        reg = comm.register(xr)
+        paths = [("staging", lambda t: comm.allreduce_(t, 1.0 / world)),
+                 ("registered", lambda t: comm.allreduce_registered_(reg, t, 1.0 / world))]
+        if nvls_ok:
+            with torch.cuda.use_mem_pool(comm.nvls_pool()):
+                xn = torch.empty(n, device="cuda")
+            off_n = comm.nvls_offset(xn)
+            paths.append(("nvls_staged", lambda t: comm.allreduce_nvls_(t, 1.0 / world)))
+            paths.append(("nvls_inplace", lambda t: comm.allreduce_nvls_inplace_(off_n, n, 1.0 / world)))
+        for name, fn in paths:
+            bufs = allreduce_inputs(world, n, 1300 + len(name))
+            t = xr if name == "registered" else (xn if name == "nvls_inplace" else torch.empty(n, device="cuda"))
+            t.copy_(torch.from_numpy(bufs[rank]))
+            fn(t)
+            counted = comm.sumsq_numel()
+            out2 = torch.empty(2, device="cuda")
+            comm.sumsq_clip_(1.0, out2)
+            torch.cuda.synchronize()
+            want = float(np.sqrt(O.grad_sumsq(t.cpu().numpy())))
+            norms = [None] * world
+            dist.all_gather_object(norms, float(out2[0]))
+            coef_ok = abs(float(out2[1]) - O.clip_coef(want, 1.0)) <= 2e-6
+            results[("sumsq", name, float(out2[0]), want)] = bool(
+                counted == n and abs(float(out2[0]) - want) <= 2e-6 * want and len(set(norms)) == 1 and coef_ok
+                and comm.sumsq_numel() == 0)
+        comm.unregister(reg)
+        comm.enable_sumsq(False)
+
         # DDP comm hook vs stock DDP on the same model / data: 3 steps, identical parameters
         def run(use_hook, nvls_buckets=False, cpp_hook=False):
             torch.manual_seed(0)
@@ -276,3 +352,222 @@ def test_real_peer_memory_allreduce_and_ddp_hook():
         assert not bad, f"rank {rank}: not bit-exact vs the rank-ordered oracle: {bad}"
         assert worst < 1e-7, f"rank {rank}: hook vs stock DDP parameters differ by {worst} beyond rtol 1e-5"
         assert same, f"rank {rank}: replicas diverged"
+
+
+# ---------------------------------------------------------------------------------------
+# the attach path of an unmodified script (launch.py + patch.py) and the clip fold, real GPUs
+# ---------------------------------------------------------------------------------------
+STAND_IN_SCRIPT = '''
+# Stand-in for the reference scripts' training logic (no valohai / accelerate imports): a DDP
+# model trained like train-accelerator.py:217-226, then a bare model trained like
+# train-task.py:288-297 with the script's OWN average_gradients (train-task.py:65-69).
+import torch
+import torch.distributed as dist
+from torch.optim import AdamW                      # train-accelerator.py:14 / train-task.py:17
+from torch.nn.parallel import DistributedDataParallel
+
+def average_gradients(model):
+    size = float(dist.get_world_size())
+    for param in model.parameters():
+        dist.all_reduce(param.grad.data, op=dist.ReduceOp.SUM)
+        param.grad.data /= size
+
+def build():
+    torch.manual_seed(0)
+    return torch.nn.Sequential(torch.nn.Linear(256, 1024), torch.nn.ReLU(), torch.nn.Linear(1024, 1536),
+                               torch.nn.ReLU(), torch.nn.Linear(1536, 64)).cuda()
+
+def train(use_ddp):
+    model = build()
+    net = DistributedDataParallel(model, device_ids=[torch.cuda.current_device()], bucket_cap_mb=2) if use_ddp else model
+    optimizer = AdamW(model.parameters(), lr=1e-3)
+    g = torch.Generator(device="cuda").manual_seed(1234 + dist.get_rank())
+    for _ in range(4):
+        loss = net(torch.randn(8, 256, device="cuda", generator=g)).square().mean()
+        loss.backward()
+        if not use_ddp:
+            average_gradients(model)
+        torch.nn.utils.clip_grad_norm_(model.parameters(), 0.05)
+        optimizer.step()
+        optimizer.zero_grad()
+    return [p.detach().clone() for p in model.parameters()], type(optimizer).__module__, net
+
+if __name__ == "__main__":
+    RESULT_DDP = train(True)
+    RESULT_TASK = train(False)
+'''
+
+
+def _attach_worker(rank, world, port, q, tmpdir):
+    import torch.distributed as dist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from distributed_llms_example_b200 import comm as comm_mod
+        from distributed_llms_example_b200 import launch, patch
+
+        path = os.path.join(tmpdir, f"stand_in_{rank}.py")
+        with open(path, "w") as f:
+            f.write(STAND_IN_SCRIPT)
+        results = {}
+        stock = launch.run_script(path, [], rebinds={}, apply_patches=False)   # the script as written
+        ours = launch.run_script(path, [])                                      # same file, plug-ins attached
+        try:
+            for key in ("RESULT_DDP", "RESULT_TASK"):
+                pa, mod_a, net_a = ours[key]
+                pb, mod_b, _ = stock[key]
+                results[(key, "optimizer_rebound", mod_a, mod_b)] = (
+                    mod_a == "distributed_llms_example_b200.optim" and mod_b.startswith("torch.optim"))
+                worst = max(float(((x - y).abs() - 1e-4 * y.abs()).max()) for x, y in zip(pa, pb))
+                results[(key, "matches_stock_run", worst)] = worst < 1e-6
+                same = True
+                for p in pa:
+                    parts = [torch.empty_like(p) for _ in range(world)]
+                    dist.all_gather(parts, p)
+                    same &= all(torch.equal(parts[0], t) for t in parts)
+                results[(key, "replicas_identical")] = same
+            ddp = ours["RESULT_DDP"][2]
+            st = getattr(ddp, "_b200_hook_state", None)
+            results[("ddp_hook_attached_by_patch", True)] = st is not None and st.total_buckets_reduced > 0
+            results[("ddp_gradient_as_bucket_view", True)] = bool(ddp.gradient_as_bucket_view)
+            results[("average_gradients_rebound", True)] = ours["average_gradients"] is launch._average_gradients
+            # the clip of the LAST steps took its norm from the all-reduce's fold, not from a second pass
+            from distributed_llms_example_b200.optim import _LIVE
+
+            results[("clip_norm_sources", tuple(sorted({o.norm_source for o in _LIVE})))] = any(
+                o.norm_source == "allreduce" for o in _LIVE)
+        finally:
+            patch.remove()
+        # clip fold-in: norm from the all-reduce equals torch.nn.utils.clip_grad_norm_ on the same grads
+        from distributed_llms_example_b200.optim import AdamW
+
+        torch.manual_seed(0)
+        model = torch.nn.Sequential(torch.nn.Linear(512, 2048), torch.nn.ReLU(), torch.nn.Linear(2048, 512)).cuda()
+        ddp = torch.nn.parallel.DistributedDataParallel(model, device_ids=[rank], bucket_cap_mb=1,
+                                                        gradient_as_bucket_view=True)
+        st = comm_mod.register_p2p_comm_hook(ddp, zero_copy_min_bytes=1 << 20)
+        opt = AdamW(model.parameters(), lr=1e-4)
+        g = torch.Generator(device="cuda").manual_seed(99 + rank)
+        ok, srcs = True, []
+        for step in range(5):
+            ddp(torch.randn(16, 512, device="cuda", generator=g)).square().mean().backward()
+            ref_norm = torch.linalg.vector_norm(torch.stack([p.grad.norm() for p in model.parameters()]))
+            got = opt.clip_grad_norm_(1e-3)
+            srcs.append(opt.norm_source)
+            ok &= abs(float(got) - float(ref_norm)) <= 2e-6 * float(ref_norm)
+            coef = float(opt.grad_scale)
+            ok &= abs(coef - min(1.0, 1e-3 / (float(ref_norm) + 1e-6))) <= 2e-6
+            opt.step(); opt.zero_grad()
+        results[("clip_from_allreduce", tuple(srcs))] = ok and srcs[0] == "kernel" and srcs[-1] == "allreduce"
+        st.comm.close()
+        q.put((rank, results, None))
+    except Exception:
+        import traceback
+
+        q.put((rank, {}, traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+def _timeout_worker(rank, world, port, q, tmpdir):
+    import time
+
+    import torch.distributed as dist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), B2_AR_TIMEOUT_MS="300")
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from distributed_llms_example_b200 import _lib as L
+        from distributed_llms_example_b200.comm import P2PComm
+
+        comm = P2PComm(staging_bytes=8 << 20)
+        x = torch.ones(1 << 20, device="cuda")
+        comm.allreduce_(x, 1.0 / world)
+        torch.cuda.synchronize()
+        comm.poll()
+        results = {("healthy_first_call", True): bool(torch.all(x == 1.0))}
+        dist.barrier()
+        late = world - 1                      # this rank "skips a bucket": it never makes call #2
+        y = torch.ones(1 << 20, device="cuda")
+        t0 = time.perf_counter()
+        if rank == late:
+            time.sleep(1.5)                   # ... and shows up for call #3 long after the others gave up
+        comm.allreduce_(y, 1.0 / world)
+        torch.cuda.synchronize()
+        raised = None
+        try:
+            comm.poll()
+        except L.B2Error as exc:
+            raised = exc.status
+        dt = time.perf_counter() - t0
+        results[("poll_raises_timeout", raised)] = raised == -4
+        results[("bucket_poisoned_not_half_reduced", True)] = bool(torch.isnan(y).all())
+        results[("within_a_second_of_the_deadline", round(dt, 2))] = dt < (3.0 if rank == late else 1.5)
+        # sticky: every later call on every rank is refused the same way, without waiting again
+        z = torch.ones(4096, device="cuda")
+        t1 = time.perf_counter()
+        comm.allreduce_(z, 1.0)
+        torch.cuda.synchronize()
+        results[("sticky", True)] = bool(torch.isnan(z).all()) and time.perf_counter() - t1 < 0.25
+        try:
+            comm.check()
+            results[("check_raises", True)] = False
+        except L.B2Error as exc:
+            results[("check_raises", True)] = exc.status == -4
+        # the optimizer refuses to apply poisoned gradients
+        from distributed_llms_example_b200.optim import AdamW
+
+        p = torch.nn.Parameter(torch.zeros(8, device="cuda"))
+        p.grad = torch.ones(8, device="cuda")
+        try:
+            AdamW([p], lr=1e-3).step()
+            results[("adamw_step_raises", True)] = False
+        except L.B2Error as exc:
+            results[("adamw_step_raises", True)] = exc.status == -4 and bool(torch.all(p == 0))
+        comm.close()
+        q.put((rank, results, None))
+    except Exception:
+        import traceback
+
+        q.put((rank, {}, traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+def _spawn(worker, tmp_path):
+    import torch.multiprocessing as mp
+
+    world = 2 if torch.cuda.device_count() < 4 else (4 if torch.cuda.device_count() < 8 else 8)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=worker, args=(r, world, port, q, str(tmp_path))) for r in range(world)]
+    for p in procs:
+        p.start()
+    outs = [q.get(timeout=600) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, results, err in outs:
+        assert err is None, f"rank {rank}:\n{err}"
+        bad = [k for k, ok in results.items() if not ok]
+        assert not bad, f"rank {rank}: {bad}"
+    return outs
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs (run with gpurun --gpus 2)")
+def test_unmodified_script_through_launcher_matches_stock_run(tmp_path):
+    """launch.run_script on a stand-in for the reference scripts (DDP loop + the script's own
+    average_gradients loop): DDP gets the hook through patch.patch_ddp, AdamW / clip_grad_norm_ /
+    average_gradients are rebound, and the trained parameters equal the unpatched run's."""
+    _spawn(_attach_worker, tmp_path)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs (run with gpurun --gpus 2)")
+def test_missing_peer_is_an_error_on_every_rank_not_bad_gradients(tmp_path):
+    """One rank skips a bucket (B2_AR_TIMEOUT_MS=300): the waiting ranks poison the bucket with NaN
+    instead of reducing half-written data, the late rank is poisoned too when it shows up, and
+    poll() / check() / AdamW.step() raise B2_ERR_TIMEOUT on every rank."""
+    _spawn(_timeout_worker, tmp_path)

@@ -106,6 +106,103 @@ def test_patch_points_rebind_and_restore():
     assert t5.CrossEntropyLoss is stock_ce and torch.optim.AdamW is stock_adamw
 
 
+def _patch_ddp_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from torch.nn.parallel import DistributedDataParallel as DDP
+
+        from distributed_llms_example_b200 import comm, patch
+
+        calls = []
+        real_register, real_wants = comm.register_p2p_comm_hook, patch._wants_hook
+        comm.register_p2p_comm_hook = lambda ddp, **kw: calls.append((ddp, kw)) or "state"
+        patch.apply(cross_entropy=False, adamw=False, fold_clip=False, comm_kwargs={"wire": "bf16"})
+        try:
+            # 1. a CPU module over gloo is left exactly as torch builds it
+            plain = DDP(torch.nn.Linear(4, 4))
+            ok_cpu = not calls and plain.gradient_as_bucket_view is False and not hasattr(plain, "_b200_hook_state")
+            # 2. a module the predicate accepts (on the GPU box: CUDA parameters, world > 1) gets the hook
+            #    exactly once, with the kwargs of patch.apply, and gradients as bucket views
+            patch._wants_hook = lambda module, kwargs: True
+            hooked = DDP(torch.nn.Linear(4, 4))
+            ok_hook = (len(calls) == 1 and calls[0][0] is hooked and calls[0][1] == {"wire": "bf16"}
+                       and hooked._b200_hook_state == "state" and hooked.gradient_as_bucket_view is True)
+            # 3. the caller's own choices win over the plug-in's defaults
+            os.environ["B2_DDP_BUCKET_MB"] = "50"
+            own = DDP(torch.nn.Linear(4, 4), gradient_as_bucket_view=False, bucket_cap_mb=7)
+            dflt = DDP(torch.nn.Linear(4, 4))
+            ok_kwargs = (own.gradient_as_bucket_view is False and own.bucket_bytes_cap == 7 * 1024 * 1024
+                         and dflt.bucket_bytes_cap == 50 * 1024 * 1024 and len(calls) == 3)
+            # 4. apply() twice does not wrap twice; remove() restores torch's constructor
+            patch.apply(cross_entropy=False, adamw=False, fold_clip=False)
+            DDP(torch.nn.Linear(4, 4))
+            ok_once = len(calls) == 4 and calls[-1][1] == {}
+        finally:
+            os.environ.pop("B2_DDP_BUCKET_MB", None)
+            patch._wants_hook = real_wants
+            comm.register_p2p_comm_hook = real_register
+            patch.remove()
+        after = DDP(torch.nn.Linear(4, 4))
+        ok_removed = len(calls) == 4 and after.gradient_as_bucket_view is False
+        q.put((rank, (ok_cpu, ok_hook, ok_kwargs, ok_once, ok_removed), None))
+    except Exception:
+        import traceback
+
+        q.put((rank, (), traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_patch_ddp_registers_the_hook_once_on_gpu_modules_only():
+    """patch.patch_ddp is how the comm hook reaches an unmodified script (accelerator.prepare and HF
+    Trainer build DistributedDataParallel themselves): the wrapped constructor must attach the hook
+    exactly once per DDP module, only where the predicate holds, and respect the caller's kwargs."""
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_patch_ddp_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    outs = [q.get(timeout=300) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, oks, err in outs:
+        assert err is None, f"rank {rank}:\n{err}"
+        assert oks and all(oks), (rank, oks)
+
+
+def test_wants_hook_predicate():
+    from distributed_llms_example_b200 import patch
+
+    assert patch._wants_hook(torch.nn.Linear(2, 2), {}) is False       # CPU parameters
+    assert patch._wants_hook(torch.nn.ReLU(), {}) is False             # no parameters at all
+
+
+def test_adamw_refuses_state_dicts_with_other_semantics():
+    """A checkpoint written by torch.optim.AdamW(amsgrad=True) must not resume here with silently
+    different optimizer semantics (the constructor rejects the flag; so must load_state_dict)."""
+    from distributed_llms_example_b200.optim import AdamW
+
+    p = torch.nn.Parameter(torch.zeros(4))
+    ref = torch.optim.AdamW([p], lr=1e-3, amsgrad=True)
+    p.grad = torch.ones(4)
+    ref.step()
+    ours = AdamW([p], lr=1e-3)
+    with pytest.raises(NotImplementedError, match="amsgrad"):
+        ours.load_state_dict(ref.state_dict())
+    assert ours.param_groups[0]["amsgrad"] is False  # refused before anything was overwritten
+    ok = torch.optim.AdamW([p], lr=1e-3)
+    ok.step()
+    ours.load_state_dict(ok.state_dict())  # a plain AdamW checkpoint still loads
+    bad = ours.state_dict()
+    bad["param_groups"][0]["maximize"] = True
+    with pytest.raises(NotImplementedError, match="maximize"):
+        ours.load_state_dict(bad)
+
+
 def test_comm_hook_signature_is_what_ddp_checks():
     from distributed_llms_example_b200.comm import p2p_allreduce_hook
 
@@ -281,6 +378,7 @@ def _vote_worker(rank, world, port, q):
             st.comm = _FakeComm(rank, world, exportable)
             st.zero_copy, st.zero_copy_min_bytes = True, 1 << 20
             st._last_seen, st._registered = {}, {}
+            st._attempts, st._never, st.max_attempts = {}, set(), 3
             st.cpp_handle = None
             return st
 
@@ -305,6 +403,16 @@ def _vote_worker(rank, world, port, q):
         st3 = state(exportable=(rank != 0))
         st3.registration_for(7, _Buf(0x4000, big))
         ok_noexport = st3.registration_for(7, _Buf(0x4000, big)) is None and not st3.comm.registered
+        # ... and that verdict is permanent on EVERY rank after one collective: later calls return
+        # without another all_gather_object (a rank that still voted would hang its peer here)
+        ok_noexport = ok_noexport and 7 in st3._never
+        for _ in range(3):
+            ok_noexport = ok_noexport and st3.registration_for(7, _Buf(0x4000, big)) is None
+        # a bucket that never settles is abandoned after max_attempts votes, on every rank alike
+        st4 = state()
+        for i in range(6):
+            st4.registration_for(9, _Buf(0x5000 + 0x100 * i * (rank == 1), big))
+        ok_noexport = ok_noexport and 9 in st4._never and not st4.comm.registered
         # a registered bucket that moves is an error, not a silent divergence
         try:
             st.registration_for(3, _Buf(0x9999, big))
@@ -458,7 +566,7 @@ def _cpp_hook_worker(rank, world, port, q):
             ddp = torch.nn.parallel.DistributedDataParallel(model)
             handle = None
             if cpp:  # no bucket is ever entered in the table: every call takes the delegation path
-                handle = mod.attach(ddp.reducer, mean_hook, None, 0, 0, 0, 1.0 / world, 0, 0)
+                handle = mod.attach(ddp.reducer, mean_hook, None, 0, 0, 0, 1.0 / world, 0, 0, 0)
             opt = torch.optim.SGD(ddp.parameters(), lr=0.1)
             g = torch.Generator().manual_seed(1234 + rank)
             for _ in range(3):
@@ -471,6 +579,17 @@ def _cpp_hook_worker(rank, world, port, q):
         ok = bool(torch.allclose(a, b, rtol=1e-6, atol=1e-8)) and len(calls) >= 3
         ok = ok and handle.slow_calls == len(calls) and handle.fast_calls == 0
         handle.set_entry(5, 0x1000, 16, 1, 4096)  # table grows on demand
+        # P2PComm.close() closes the handle: a later backward raises instead of using a freed communicator
+        handle.close()
+        try:
+            torch.manual_seed(0)
+            m2 = torch.nn.parallel.DistributedDataParallel(torch.nn.Linear(8, 8))
+            h2 = mod.attach(m2.reducer, mean_hook, None, 0, 0, 0, 1.0 / world, 0, 0, 0)
+            h2.close()
+            m2(torch.randn(2, 8)).sum().backward()
+            ok = False
+        except RuntimeError as exc:
+            ok = ok and "closed" in str(exc)
         q.put((rank, ok, None))
     except Exception:
         import traceback

@@ -8,12 +8,15 @@ a fixed array inside libb2ddp.so, and this entry point takes inputs and outputs 
 What is checked, through the C ABI: on two calls in a row (different shapes, so the second
 call finds the first call's leftovers in the shared array) the loss, the per-row
 log-sum-exp and the valid-row count equal those of b2_ce_forward with a caller workspace,
-within the 1e-5 relative tolerance the other cross-entropy tests use; a request above the
-stated row limit is refused with B2_ERR_TOO_LARGE. The file is named so that pytest collects
+and those of the CPU oracle (oracle/ref_numpy.py ce_forward) on the same values, within the
+1e-5 relative tolerance the other cross-entropy tests use; a request above the stated row
+limit is refused with B2_ERR_TOO_LARGE. The file is named so that pytest collects
 it last; it also passes when run alone in a fresh process."""
 import numpy as np
 import pytest
 import torch
+
+from oracle import ref_numpy as O
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
@@ -53,6 +56,11 @@ def test_noalloc_forward_matches_workspace_forward_twice_in_a_row():
         np.testing.assert_allclose(got[1], ref[1], rtol=1e-5)   # loss
         assert got[2][0] == ref[2][0] == float((y != -100).sum())  # n_valid
         assert np.isfinite(got[1][0])
+        # ... and it stands on its own against the oracle, not only against its sibling entry point
+        o_loss, o_lse, o_nvalid = O.ce_forward(z.float().cpu().numpy(), y.cpu().numpy())
+        np.testing.assert_allclose(got[0], o_lse, rtol=1e-5)
+        np.testing.assert_allclose(got[1][0], o_loss, rtol=1e-5)
+        assert got[2][0] == o_nvalid
 
 
 def test_noalloc_rejects_more_rows_than_its_scratch_holds():
