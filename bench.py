@@ -401,18 +401,35 @@ def grad_sync_parity(comm, world: int, rank: int, dev) -> dict:
 
 def loss_parity(args, local_rank: int, steps: int = 4) -> dict:
     """This arm against the stock arm on the headline config with dropout 0, the same seeds and the
-    same batches: `steps` optimizer steps each, loss per step compared (<= 2e-4 relative: bf16
-    autocast GEMMs are identical in both arms; the arms differ in CE, clip, AdamW and the
-    all-reduce's summation order)."""
+    same batches: `steps` optimizer steps each, loss per step compared. Two bars:
+      * step 0 (identical parameters, identical bf16 logits in both arms) against an fp32
+        cross-entropy of the stock model's own logits: <= 2e-5 relative. This isolates the loss
+        kernel from torch's bf16-autocast cross-entropy, which carries ~1e-3 of its own error
+        (measured here as `stock_ce_own_error`);
+      * every step against the stock arm's reported loss: <= 1e-3 relative, the size of that error
+        (the arms also differ in clip, AdamW and the all-reduce's summation order, all <= 1e-6)."""
+    import torch.nn.functional as F
+
     from distributed_llms_example_b200.harness import StepConfig, StepHarness
 
     losses = {}
+    ce32 = None
     for impl in ("b200", "stock"):
         cfg = StepConfig(model=args.model, semantics=args.semantics, impl=impl, device=f"cuda:{local_rank}",
                          batch_size=args.batch_size, grad_accum=args.grad_accum, label_mode=args.label_mode,
                          bf16=True, dropout=0.0, wire="fp32", bucket_cap_mb=args.bucket_cap_mb, total_steps=1000)
         h = StepHarness(cfg)
         host = h.host_batches(steps * args.grad_accum, seed=4321)
+        if impl == "stock":
+            with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+                vals = []
+                for mb in host[:args.grad_accum]:
+                    out = h.model(**h.to_device(mb))
+                    lab = mb["labels"].to(h.device).view(-1)
+                    vals.append(float(F.cross_entropy(out.logits.float().view(-1, out.logits.size(-1)), lab,
+                                                      ignore_index=-100)))
+                    del out
+                ce32 = sum(vals) / len(vals)
         ls = []
         for i in range(steps):
             ls.append(float(h.step(host[i * args.grad_accum:(i + 1) * args.grad_accum]).item()))
@@ -421,8 +438,11 @@ def loss_parity(args, local_rank: int, steps: int = 4) -> dict:
         del h
         torch.cuda.empty_cache()
     rel = [abs(a - b) / max(abs(b), 1e-30) for a, b in zip(losses["b200"], losses["stock"])]
+    step0 = abs(losses["b200"][0] - ce32) / abs(ce32)
     return {"steps": steps, "b200": losses["b200"], "stock": losses["stock"], "max_rel": max(rel),
-            "tolerance": 2e-4, "ok": bool(max(rel) <= 2e-4), "dropout": 0.0}
+            "tolerance": 1e-3, "step0_fp32_ce_of_stock_logits": ce32, "step0_rel_vs_fp32_ce": step0,
+            "step0_tolerance": 2e-5, "stock_ce_own_error": abs(losses["stock"][0] - ce32) / abs(ce32),
+            "ok": bool(max(rel) <= 1e-3 and step0 <= 2e-5), "dropout": 0.0}
 
 
 def adamw_traffic(model: str):
@@ -574,7 +594,16 @@ def main():
     if world > 1:
         # optional extras must never cost the headline numbers above
         try:
-            out["grad_sync"] = grad_sync_probe(h, args.impl, world)
+            # the size the Reducer's buckets really have in this run (the median registered bucket),
+            # and torch's 25 MiB default for reference
+            mb = 25.0
+            if h.hook_state is not None and h.hook_state._registered:
+                mb = statistics.median(r_[1] for r_ in h.hook_state._registered.values()) * 4 / (1 << 20)
+            elif args.bucket_cap_mb:
+                mb = args.bucket_cap_mb
+            out["grad_sync"] = grad_sync_probe(h, args.impl, world, bucket_mb=mb)
+            if abs(mb - 25.0) > 1.0:
+                out["grad_sync"]["at_25_mib"] = grad_sync_probe(h, args.impl, world, bucket_mb=25.0)
             if h.hook_state is not None:  # which path the Reducer's buckets actually took
                 regs = h.hook_state._registered.values()
                 out["grad_sync"]["ddp_buckets"] = {

@@ -222,6 +222,82 @@ def bench_ce_kernel(args):
 
 
 # ------------------------------------------------------------------------------------------
+def bench_lmce(args):
+    """Fused lm_head + CE (tcgen05) next to what it replaces: a bf16 library GEMM writing the
+    [N, V] logits followed by this repo's CE kernels, and by ATen's. d_model 1024, vocab 32128.
+    Tensor-pipe roofline: 2*N*V*D flop per pass against MEASURED_PEAKS.json bf16_tflops (burst)."""
+    import torch.nn.functional as F
+
+    from distributed_llms_example_b200 import _lib as L
+    from distributed_llms_example_b200.loss import cross_entropy
+
+    lib = L.load()
+    v, d = 32128, args.d_model
+    peak_tf = 1654.5
+    try:
+        peak_tf = float(json.loads((ROOT / "MEASURED_PEAKS.json").read_text())["bf16_tflops"])
+    except Exception:
+        pass
+    stream = torch.cuda.current_stream().cuda_stream
+    for n in args.rows:
+        torch.manual_seed(0)
+        h = torch.randn(n, d, device="cuda").to(torch.bfloat16)
+        w = (torch.randn(v, d, device="cuda") * (4.0 / d ** 0.5)).to(torch.bfloat16)
+        y = torch.randint(0, v, (n,), device="cuda")
+        y[torch.rand(n, device="cuda") < 0.2] = -100
+        lse = torch.empty(n, device="cuda")
+        loss = torch.empty(1, device="cuda")
+        nvalid = torch.empty(1, device="cuda")
+        g = torch.ones(1, device="cuda")
+        nb = lib.b2_lmce_workspace_bytes(n, v)
+        ws = torch.zeros(nb, dtype=torch.uint8, device="cuda")
+        ld = (v + 7) // 8 * 8
+        dz = torch.empty(n, ld, dtype=torch.bfloat16, device="cuda")
+
+        def fused_fwd():
+            L.check(lib.b2_lmce_forward(h.data_ptr(), w.data_ptr(), y.data_ptr(), n, v, d, -100, 1, lse.data_ptr(),
+                                        loss.data_ptr(), nvalid.data_ptr(), ws.data_ptr(), nb, stream))
+
+        def fused_bwd():
+            L.check(lib.b2_lmce_backward_dlogits(h.data_ptr(), w.data_ptr(), y.data_ptr(), lse.data_ptr(), g.data_ptr(),
+                                                 nvalid.data_ptr(), n, v, d, -100, 1, dz.data_ptr(), ld, stream))
+
+        def gemm_only():
+            return F.linear(h, w)
+
+        def unfused_b200_fwd():
+            return cross_entropy(F.linear(h, w), y)
+
+        def unfused_aten_fwd():
+            return F.cross_entropy(F.linear(h, w).float(), y, ignore_index=-100)
+
+        hz = h.clone().requires_grad_(True)
+
+        def unfused_b200_fwd_bwd_dlogits():
+            z = F.linear(hz.detach(), w).requires_grad_(True)
+            cross_entropy(z, y).backward()
+            return z.grad
+
+        flop = 2.0 * n * v * d
+        flush = n * v * 2 < (200 << 20)
+        rec = {"bench": "lmce", "rows": n, "vocab": v, "d_model": d, "flop_per_pass": flop}
+        for name, fn in (("fused_fwd", fused_fwd), ("fused_bwd_dlogits", fused_bwd), ("cublas_gemm_only", gemm_only),
+                         ("unfused_gemm_plus_b200_ce_fwd", unfused_b200_fwd),
+                         ("unfused_gemm_plus_aten_ce_fwd", unfused_aten_fwd),
+                         ("unfused_gemm_plus_b200_ce_fwd_bwd_dlogits", unfused_b200_fwd_bwd_dlogits)):
+            if args.only == "ours" and not name.startswith("fused"):
+                continue
+            med, best = time_ms(fn, args.iters, args.warmup, flush)
+            rec[name + "_us"] = med * 1e3
+            if name in ("fused_fwd", "fused_bwd_dlogits", "cublas_gemm_only"):
+                rec[name + "_tflops"] = flop / (med / 1e3) / 1e12
+                rec[name + "_frac_of_measured_bf16_peak"] = flop / (med / 1e3) / 1e12 / peak_tf
+        emit(**rec)
+        del h, w, dz
+        torch.cuda.empty_cache()
+
+
+# ------------------------------------------------------------------------------------------
 def bench_allreduce_emulated(args):
     """One GPU, W virtual ranks in ONE cooperative launch (b2_allreduce_emulated): the same device
     code as the multi-GPU kernels, runnable under ncu (which must never wrap a multi-rank command).
@@ -327,7 +403,8 @@ def bench_allreduce(args):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("bench", choices=["adamw", "ce", "ce_kernel", "allreduce", "allreduce_emulated"])
+    ap.add_argument("bench", choices=["adamw", "ce", "ce_kernel", "lmce", "allreduce", "allreduce_emulated"])
+    ap.add_argument("--d-model", type=int, default=1024)
     ap.add_argument("--models", nargs="+", default=["t5-small", "flan-t5-base", "flan-t5-large", "flan-t5-xl"])
     ap.add_argument("--rows", nargs="+", type=int, default=[128, 1024, 8192, 32768])
     ap.add_argument("--sizes-mb", nargs="+", type=float, default=[1, 2, 4, 8, 16, 25, 32, 64, 128, 256, 512, 1024])
@@ -338,7 +415,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--only", default="all", choices=["all", "ours"])
     args = ap.parse_args()
-    {"adamw": bench_adamw, "ce": bench_ce, "ce_kernel": bench_ce_kernel, "allreduce": bench_allreduce,
+    {"adamw": bench_adamw, "ce": bench_ce, "ce_kernel": bench_ce_kernel, "lmce": bench_lmce, "allreduce": bench_allreduce,
      "allreduce_emulated": bench_allreduce_emulated}[args.bench](args)
 
 

@@ -46,6 +46,10 @@ SIGNATURES = {
     "b2_ce_forward": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _i32, _vp, _vp, _vp, _vp, _sz, _vp]),
     "b2_ce_forward_noalloc": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _i32, _vp, _vp, _vp, _vp]),
     "b2_ce_backward": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _i32, _vp, _vp]),
+    "b2_lmce_workspace_bytes": (_sz, [_i64, _i64]),
+    "b2_lmce_forward": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _i64, _i32, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "b2_lmce_backward_dlogits": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _i32, _vp, _i64,
+                                           _vp]),
     "b2_adamw_plan": (_i64, [C.POINTER(AdamWTensor), C.c_int32]),
     "b2_adamw_step": (C.c_int, [_vp, C.c_int32, _i64, C.POINTER(AdamWHyper), C.c_int32, _vp, _vp]),
     "b2_adamw_step_flat": (C.c_int, [_vp, _vp, _vp, _vp, _i64, C.POINTER(AdamWHyper), _vp, _vp]),

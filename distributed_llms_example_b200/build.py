@@ -21,7 +21,7 @@ INCLUDE = PKG_DIR.parent / "include"
 LIB_PATH = PKG_DIR / "libb2ddp.so"
 _STAMP = PKG_DIR / ".libb2ddp.stamp"
 
-SOURCES = ["error.cu", "adamw.cu", "cross_entropy.cu", "gradnorm.cu", "allreduce.cu", "nvls.cu"]
+SOURCES = ["error.cu", "adamw.cu", "cross_entropy.cu", "lmhead_ce.cu", "gradnorm.cu", "allreduce.cu", "nvls.cu"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -113,6 +113,14 @@ class CrossEntropyLoss(nn.Module):
         self.label_smoothing = 0.0
 
     def forward(self, input: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+        if type(input) is not torch.Tensor:
+            # lazy logits from a patched lm_head (fused.py): the logits are never materialised,
+            # the matmul and the loss run as one tensor-core kernel
+            from .fused import fused_lm_head_ce, lazy_parts
+
+            parts = lazy_parts(input)
+            if parts is not None:
+                return fused_lm_head_ce(parts[0], parts[1], target, self.ignore_index)
         return cross_entropy(input, target, self.ignore_index)
 
     def extra_repr(self) -> str:

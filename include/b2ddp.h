@@ -100,6 +100,40 @@ int b2_ce_backward(const void* logits, const int64_t* labels, const float* row_l
                    void* dlogits, b2_stream_t stream);
 
 /* ------------------------------------------------------------------------- *
+ * (c') fused lm_head + cross-entropy on the tensor cores
+ *
+ * Replaces, for T5-family models, the pair
+ *     lm_logits = self.lm_head(sequence_output)          (SP/transformers/models/t5/modeling_t5.py:1110)
+ *     loss = CrossEntropyLoss(ignore_index=-100)(lm_logits.view(-1, V), labels.view(-1))   (:1112-1117)
+ * reached from train-accelerator.py:220-221, train-task.py:289-290 and train-torchrun.py:140: the
+ * [n_rows, vocab] logits are produced tile by tile by tcgen05.mma (bf16 x bf16 -> fp32 in TMEM,
+ * operands staged by TMA) and consumed by the cross-entropy epilogue straight out of TMEM, so
+ * they never reach HBM in the forward pass.
+ *   hidden [n_rows, d_model] bf16 row-major (the lm_head input, already scaled by d_model^-0.5
+ *          where the model ties its embeddings), weight [vocab, d_model] bf16 row-major
+ *          (nn.Linear layout), labels [n_rows] int64; d_model a multiple of 64; bases 16-byte aligned.
+ *   round_bf16 != 0: each logit is rounded to bf16 before the softmax - bit-for-bit what the
+ *          unfused path computes from its bf16 logits tensor; 0 keeps the fp32 accumulator.
+ * Outputs as b2_ce_forward: row_lse[n_rows], loss_out[1] (NaN when no row is valid),
+ * nvalid_out[1]. workspace: b2_lmce_workspace_bytes(n_rows, vocab) bytes, 16-byte aligned, its
+ * first 16 bytes zero before the first call (the kernel leaves them zero). Deterministic.
+ * ------------------------------------------------------------------------- */
+size_t b2_lmce_workspace_bytes(int64_t n_rows, int64_t vocab);
+int b2_lmce_forward(const void* hidden, const void* weight, const int64_t* labels, int64_t n_rows,
+                    int64_t vocab, int64_t d_model, int64_t ignore_index, int round_bf16,
+                    float* row_lse, float* loss_out, float* nvalid_out, void* workspace,
+                    size_t workspace_bytes, b2_stream_t stream);
+/* Backward of the same pair (loss.backward() at train-accelerator.py:222 / train-task.py:292): the
+ * logits tile is recomputed by the same tcgen05 main loop and the epilogue writes
+ *   dlogits[i, j] = (exp(z_ij - lse_i) - [j == y_i]) * grad_out / n_valid      (0 on ignored rows)
+ * in bf16 with row pitch `row_stride` elements (>= vocab, multiple of 8). The caller forms
+ * d hidden = dlogits @ weight and d weight = dlogits^T @ hidden with library GEMMs. */
+int b2_lmce_backward_dlogits(const void* hidden, const void* weight, const int64_t* labels,
+                             const float* row_lse, const float* grad_out, const float* nvalid,
+                             int64_t n_rows, int64_t vocab, int64_t d_model, int64_t ignore_index,
+                             int round_bf16, void* dlogits, int64_t row_stride, b2_stream_t stream);
+
+/* ------------------------------------------------------------------------- *
  * (b) AdamW step over many tensors in one launch
  *
  * Replaces torch.optim.AdamW.step (SP/torch/optim/adam.py:215-272 -> _single_tensor_adam

@@ -52,3 +52,24 @@ def collate_inputs(b: int, mode: str, seed: int = 41, src_len: int = 64, tgt_len
             tgt = tgt + [0] * (tgt_len - len(tgt))
         feats.append({"input_ids": src, "attention_mask": attn, "labels": tgt})
     return feats
+
+
+def lmce_inputs(n: int, v: int, d: int, seed: int, frac_ignored: float):
+    """lm_head input [n, d] ~ N(0,1) and weight [v, d] ~ N(0, 4/sqrt(d)), both already rounded to
+    bf16 values (stored as fp32), so logits ~ N(0, 4) like the CE microbench tensors; labels
+    uniform in [0, v) with -100 on a per-row basis."""
+    rs = np.random.RandomState(seed)
+
+    def bf16(x):
+        u = x.astype(np.float32).view(np.uint32).astype(np.uint64)
+        return ((u + 0x7FFF + ((u >> 16) & 1)) & 0xFFFF0000).astype(np.uint32).view(np.float32)
+
+    hidden = bf16(rs.standard_normal((n, d)))
+    weight = bf16(rs.standard_normal((v, d)) * (4.0 / np.sqrt(d)))
+    labels = rs.randint(0, v, size=n).astype(np.int64)
+    if frac_ignored >= 1.0:
+        labels[:] = -100
+    elif frac_ignored > 0:
+        k = max(1, int(round(n * frac_ignored)))
+        labels[rs.permutation(n)[:k]] = -100
+    return hidden, weight, labels

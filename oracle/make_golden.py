@@ -17,7 +17,7 @@ ROOT = Path(__file__).resolve().parent.parent
 sys.path.insert(0, str(ROOT))
 
 from oracle import torch_ref  # noqa: E402
-from oracle.inputs import adamw_inputs, allreduce_inputs, ce_inputs, collate_inputs  # noqa: E402
+from oracle.inputs import adamw_inputs, allreduce_inputs, ce_inputs, collate_inputs, lmce_inputs  # noqa: E402
 
 GOLD = ROOT / "tests" / "golden"
 
@@ -60,6 +60,41 @@ CE_CASES = {
     "all_ignored_fp32": (4, 512, 16, 1.0, "fp32"),      # NaN loss, zero gradient
     "single_row_bf16": (1, 32128, 17, 0.0, "bf16"),
 }
+
+
+LMCE_CASES = {
+    # name: (rows, vocab, d_model, seed, fraction of -100 labels); shapes ragged against the
+    # kernel's 128 x 256 x 64 tiles on purpose
+    "small": (200, 1000, 128, 51, 0.25),
+    "one_tile": (130, 300, 64, 52, 0.1),
+    "all_ignored": (64, 512, 64, 53, 1.0),
+}
+
+
+def gen_lmce():
+    """torch's own ops as the scripts reach them under bf16 autocast: a bf16 F.linear (fp32
+    accumulation, bf16 output), then F.cross_entropy on the up-cast logits, then autograd."""
+    import torch.nn.functional as F
+
+    out = {}
+    for name, (n, v, d, seed, frac) in LMCE_CASES.items():
+        hidden, weight, labels = lmce_inputs(n, v, d, seed, frac)
+        h = torch.from_numpy(hidden).to(torch.bfloat16).requires_grad_(True)
+        w = torch.from_numpy(weight).to(torch.bfloat16).requires_grad_(True)
+        logits = F.linear(h, w)
+        assert logits.dtype == torch.bfloat16
+        z32 = logits.float()
+        z32.retain_grad()
+        loss = F.cross_entropy(z32, torch.from_numpy(labels), ignore_index=-100)
+        out[f"{name}/loss"] = loss.detach().numpy()
+        out[f"{name}/row_lse"] = torch.logsumexp(z32.detach(), dim=1).numpy()
+        if frac < 1.0:
+            loss.backward()
+            out[f"{name}/dlogits"] = z32.grad.numpy()
+            out[f"{name}/dhidden"] = h.grad.float().numpy()   # bf16 GEMM outputs, as the library gives them
+            out[f"{name}/dweight"] = w.grad.float().numpy()
+        out[f"{name}/meta"] = np.array([n, v, d, seed, int(frac * 100)], dtype=np.int64)
+    np.savez_compressed(GOLD / "lmce.npz", **out)
 
 
 ADAMW_CASES = {
@@ -127,5 +162,6 @@ if __name__ == "__main__":
     gen_adamw()
     gen_allreduce()
     gen_collate()
+    gen_lmce()
     for f in sorted(GOLD.glob("*.npz")):
         print(f.name, f.stat().st_size, "bytes")

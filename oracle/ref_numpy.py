@@ -103,6 +103,35 @@ def linear_schedule_factor(current_step: int, num_warmup_steps: int, num_trainin
 
 
 # --------------------------------------------------------------------------------------
+# (8f row 4) lm_head + cross-entropy as one op
+#   reference: outputs = model(**batch); loss = outputs.loss at train-accelerator.py:220-221,
+#              train-task.py:289-290, train-torchrun.py:140
+#   library  : lm_logits = self.lm_head(sequence_output) then CrossEntropyLoss(ignore_index=-100)
+#              (SP/transformers/models/t5/modeling_t5.py:1110-1117); under bf16 autocast the
+#              matmul accumulates in fp32 and its output is rounded to bf16
+# --------------------------------------------------------------------------------------
+def lm_head_logits(hidden: np.ndarray, weight: np.ndarray, round_bf16: bool = True) -> np.ndarray:
+    """hidden [N, D] @ weight[V, D]^T in float64 from bf16-valued inputs; with round_bf16 the result
+    is rounded to bf16 (via fp32) like the library's bf16 GEMM output. Returned as float32."""
+    z = (np.asarray(hidden, dtype=np.float64) @ np.asarray(weight, dtype=np.float64).T).astype(F32)
+    return _round_bf16(z) if round_bf16 else z
+
+
+def lm_head_ce_forward(hidden, weight, labels, ignore_index: int = -100, round_bf16: bool = True):
+    """(loss, row_lse, n_valid) of ce_forward on lm_head_logits."""
+    return ce_forward(lm_head_logits(hidden, weight, round_bf16), labels, ignore_index)
+
+
+def lm_head_ce_backward(hidden, weight, labels, grad_out: float = 1.0, ignore_index: int = -100,
+                        round_bf16: bool = True):
+    """(dlogits, d hidden, d weight) in float64 math: dlogits from ce_backward, then the two
+    contractions the chain rule gives (the bf16 rounding of the logits is treated as identity,
+    as autograd treats the cast)."""
+    dz = ce_backward(lm_head_logits(hidden, weight, round_bf16), labels, grad_out, ignore_index).astype(np.float64)
+    return dz, dz @ np.asarray(weight, dtype=np.float64), dz.T @ np.asarray(hidden, dtype=np.float64)
+
+
+# --------------------------------------------------------------------------------------
 # (a3/a4) gradient mean all-reduce
 #   reference: DDP Reducer via train-accelerator.py:189,222 / train-torchrun.py:127,140, and
 #              train-task.py:65-69 (all_reduce SUM then "/= size")

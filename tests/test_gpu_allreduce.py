@@ -390,7 +390,7 @@ def train(use_ddp):
         torch.nn.utils.clip_grad_norm_(model.parameters(), 0.05)
         optimizer.step()
         optimizer.zero_grad()
-    return [p.detach().clone() for p in model.parameters()], type(optimizer).__module__, net
+    return [p.detach().clone() for p in model.parameters()], type(optimizer).__module__, net, optimizer
 
 if __name__ == "__main__":
     RESULT_DDP = train(True)
@@ -416,8 +416,8 @@ def _attach_worker(rank, world, port, q, tmpdir):
         ours = launch.run_script(path, [])                                      # same file, plug-ins attached
         try:
             for key in ("RESULT_DDP", "RESULT_TASK"):
-                pa, mod_a, net_a = ours[key]
-                pb, mod_b, _ = stock[key]
+                pa, mod_a, net_a, opt_a = ours[key]
+                pb, mod_b, _, _ = stock[key]
                 results[(key, "optimizer_rebound", mod_a, mod_b)] = (
                     mod_a == "distributed_llms_example_b200.optim" and mod_b.startswith("torch.optim"))
                 worst = max(float(((x - y).abs() - 1e-4 * y.abs()).max()) for x, y in zip(pa, pb))
@@ -434,15 +434,14 @@ def _attach_worker(rank, world, port, q, tmpdir):
             results[("ddp_gradient_as_bucket_view", True)] = bool(ddp.gradient_as_bucket_view)
             results[("average_gradients_rebound", True)] = ours["average_gradients"] is launch._average_gradients
             # the clip of the LAST steps took its norm from the all-reduce's fold, not from a second pass
-            from distributed_llms_example_b200.optim import _LIVE
-
-            results[("clip_norm_sources", tuple(sorted({o.norm_source for o in _LIVE})))] = any(
-                o.norm_source == "allreduce" for o in _LIVE)
+            srcs = (ours["RESULT_DDP"][3].norm_source, ours["RESULT_TASK"][3].norm_source)
+            results[("clip_norm_sources", srcs)] = srcs == ("allreduce", "allreduce")
         finally:
             patch.remove()
         # clip fold-in: norm from the all-reduce equals torch.nn.utils.clip_grad_norm_ on the same grads
         from distributed_llms_example_b200.optim import AdamW
 
+        comm_mod.default_comm().enable_sumsq(False)  # as a fresh process would start
         torch.manual_seed(0)
         model = torch.nn.Sequential(torch.nn.Linear(512, 2048), torch.nn.ReLU(), torch.nn.Linear(2048, 512)).cuda()
         ddp = torch.nn.parallel.DistributedDataParallel(model, device_ids=[rank], bucket_cap_mb=1,

@@ -133,7 +133,9 @@ def _patch_ddp_worker(rank, world, port, q):
             own = DDP(torch.nn.Linear(4, 4), gradient_as_bucket_view=False, bucket_cap_mb=7)
             dflt = DDP(torch.nn.Linear(4, 4))
             ok_kwargs = (own.gradient_as_bucket_view is False and own.bucket_bytes_cap == 7 * 1024 * 1024
-                         and dflt.bucket_bytes_cap == 50 * 1024 * 1024 and len(calls) == 3)
+                         and dflt.bucket_bytes_cap == 50 * 1024 * 1024 and len(calls) == 3
+                         and hooked.bucket_bytes_cap == 128 * 1024 * 1024     # the plug-in's own default
+                         and plain.bucket_bytes_cap == 25 * 1024 * 1024)      # torch's, untouched
             # 4. apply() twice does not wrap twice; remove() restores torch's constructor
             patch.apply(cross_entropy=False, adamw=False, fold_clip=False)
             DDP(torch.nn.Linear(4, 4))
