@@ -75,6 +75,8 @@ def parse_args():
     ap.add_argument("--no-stock", action="store_true", help="skip the stock-GPU leg (vs_baseline stays null)")
     ap.add_argument("--no-parity", action="store_true", help="skip the N>1 parity block and the loss comparison")
     ap.add_argument("--dropout", type=float, default=0.1)
+    ap.add_argument("--fused-lm-head", type=int, default=None, choices=[0, 1],
+                    help="b200 arm: lm_head + CE as one tcgen05 kernel (default: B2_FUSED_LM_HEAD)")
     return ap.parse_args()
 
 
@@ -417,7 +419,8 @@ def loss_parity(args, local_rank: int, steps: int = 4) -> dict:
     for impl in ("b200", "stock"):
         cfg = StepConfig(model=args.model, semantics=args.semantics, impl=impl, device=f"cuda:{local_rank}",
                          batch_size=args.batch_size, grad_accum=args.grad_accum, label_mode=args.label_mode,
-                         bf16=True, dropout=0.0, wire="fp32", bucket_cap_mb=args.bucket_cap_mb, total_steps=1000)
+                         bf16=True, dropout=0.0, wire="fp32", bucket_cap_mb=args.bucket_cap_mb, total_steps=1000,
+                         fused_lm_head=None if args.fused_lm_head is None else bool(args.fused_lm_head))
         h = StepHarness(cfg)
         host = h.host_batches(steps * args.grad_accum, seed=4321)
         if impl == "stock":
@@ -472,7 +475,8 @@ def run_gpu_arm(args, impl: str, world: int, local_rank: int, K: int, W: int, wi
     cfg = StepConfig(model=args.model, semantics=args.semantics, impl=impl, device=f"cuda:{local_rank}",
                      batch_size=args.batch_size, grad_accum=args.grad_accum, label_mode=args.label_mode,
                      bf16=True, wire=args.wire, bucket_cap_mb=args.bucket_cap_mb, dropout=args.dropout,
-                     total_steps=max(1000, 4 * (K + W)))
+                     total_steps=max(1000, 4 * (K + W)),
+                     fused_lm_head=None if args.fused_lm_head is None else bool(args.fused_lm_head))
     h = StepHarness(cfg)
     ga = args.grad_accum
     host = h.host_batches((2 * K + W) * ga)
@@ -590,6 +594,10 @@ def main():
            "params": n_params, "lib": str(_lib.lib_path().name) if args.impl == "b200" else None}
     if args.impl == "b200" and args.semantics == "trainer":
         out["clip_norm_source"] = h.optimizer.norm_source
+    if args.impl == "b200":
+        from distributed_llms_example_b200 import patch as _patch
+
+        out["fused_lm_head_ce"] = "t5_forward" in _patch._saved
     failed = False
     if world > 1:
         # optional extras must never cost the headline numbers above

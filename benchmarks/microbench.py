@@ -212,10 +212,16 @@ def bench_ce_kernel(args):
 
             fwd(0)
             f_ms, b_ms = run(fwd), run(bwd)
+            poly_ms = None
+            if tdt is torch.bfloat16:  # same process, same buffers: MUFU-only vs a quarter on the FMA pipe
+                os.environ["B2_CE_POLY"] = "1" if os.environ.get("B2_CE_POLY") != "1" else "0"
+                poly_ms = run(fwd)
+                os.environ["B2_CE_POLY"] = "1" if os.environ.get("B2_CE_POLY") != "1" else "0"
             fb, bb = n * v * s, n * v * s * (1 + frac_valid)
             emit(bench="ce_kernel", dtype=str(tdt).split(".")[-1], rows=n, buffers=nbuf, reps=reps,
                  fwd_us=f_ms * 1e3, bwd_us=b_ms * 1e3, fwd_gbs=fb / f_ms / 1e6, bwd_gbs=bb / b_ms / 1e6,
                  fwd_frac_measured_peak=fb / f_ms / 1e6 / PEAK, bwd_frac_measured_peak=bb / b_ms / 1e6 / PEAK,
+                 fwd_us_other_exp_mode=None if poly_ms is None else poly_ms * 1e3,
                  env={k: os.environ[k] for k in os.environ if k.startswith("B2_CE")})
             del zs, ds
             torch.cuda.empty_cache()
@@ -256,7 +262,23 @@ def bench_lmce(args):
 
         def fused_fwd():
             L.check(lib.b2_lmce_forward(h.data_ptr(), w.data_ptr(), y.data_ptr(), n, v, d, -100, 1, lse.data_ptr(),
-                                        loss.data_ptr(), nvalid.data_ptr(), ws.data_ptr(), nb, stream))
+                                        loss.data_ptr(), nvalid.data_ptr(), None, 0, ws.data_ptr(), nb, stream))
+
+        zst = torch.empty(n, ld, dtype=torch.bfloat16, device="cuda")
+
+        def fused_fwd_store():
+            L.check(lib.b2_lmce_forward(h.data_ptr(), w.data_ptr(), y.data_ptr(), n, v, d, -100, 1, lse.data_ptr(),
+                                        loss.data_ptr(), nvalid.data_ptr(), zst.data_ptr(), ld, ws.data_ptr(), nb,
+                                        stream))
+
+        def fused_fwd_store_plus_ce_bwd():
+            fused_fwd_store()
+            L.check(lib.b2_ce_backward(zst.data_ptr(), y.data_ptr(), lse.data_ptr(), g.data_ptr(), nvalid.data_ptr(), n,
+                                       v, ld, -100, L.B2_BF16, dz.data_ptr(), stream))
+
+        def fused_fwd_plus_recompute_bwd():
+            fused_fwd()
+            fused_bwd()
 
         def fused_bwd():
             L.check(lib.b2_lmce_backward_dlogits(h.data_ptr(), w.data_ptr(), y.data_ptr(), lse.data_ptr(), g.data_ptr(),
@@ -281,7 +303,11 @@ def bench_lmce(args):
         flop = 2.0 * n * v * d
         flush = n * v * 2 < (200 << 20)
         rec = {"bench": "lmce", "rows": n, "vocab": v, "d_model": d, "flop_per_pass": flop}
-        for name, fn in (("fused_fwd", fused_fwd), ("fused_bwd_dlogits", fused_bwd), ("cublas_gemm_only", gemm_only),
+        for name, fn in (("fused_fwd", fused_fwd), ("fused_fwd_store", fused_fwd_store),
+                         ("fused_bwd_dlogits", fused_bwd),
+                         ("fused_fwd_store_plus_ce_bwd", fused_fwd_store_plus_ce_bwd),
+                         ("fused_fwd_plus_recompute_bwd", fused_fwd_plus_recompute_bwd),
+                         ("cublas_gemm_only", gemm_only),
                          ("unfused_gemm_plus_b200_ce_fwd", unfused_b200_fwd),
                          ("unfused_gemm_plus_aten_ce_fwd", unfused_aten_fwd),
                          ("unfused_gemm_plus_b200_ce_fwd_bwd_dlogits", unfused_b200_fwd_bwd_dlogits)):
@@ -289,7 +315,7 @@ def bench_lmce(args):
                 continue
             med, best = time_ms(fn, args.iters, args.warmup, flush)
             rec[name + "_us"] = med * 1e3
-            if name in ("fused_fwd", "fused_bwd_dlogits", "cublas_gemm_only"):
+            if name in ("fused_fwd", "fused_fwd_store", "fused_bwd_dlogits", "cublas_gemm_only"):
                 rec[name + "_tflops"] = flop / (med / 1e3) / 1e12
                 rec[name + "_frac_of_measured_bf16_peak"] = flop / (med / 1e3) / 1e12 / peak_tf
         emit(**rec)
@@ -401,9 +427,76 @@ def bench_allreduce(args):
         dist.destroy_process_group()
 
 
+def bench_allreduce_tune(args):
+    """Event-timed sweep of the zero-copy all-reduce kernels' launch shape (CTAs x packs per thread x
+    loads in flight) at DDP-sized buckets: ncu must not wrap multi-rank commands, so this table is the
+    tuning evidence for the NVLink-bound kernels. One JSON line per (path, size, shape)."""
+    from distributed_llms_example_b200.comm import P2PComm
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    comm = P2PComm(staging_bytes=args.staging_mb << 20)
+    nvls = comm.enable_nvls((int(sum(args.sizes_mb) * 1.1) + 256) << 20)
+    pool = comm.nvls_pool() if nvls else None
+
+    def timed(fn, iters, warmup=3):
+        for _ in range(warmup):
+            fn()
+        torch.cuda.synchronize()
+        dist.barrier()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(iters):
+            fn()
+        b.record()
+        b.synchronize()
+        t = torch.tensor([a.elapsed_time(b) / iters], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    for sumsq in (False, True):
+        comm.enable_sumsq(sumsq)
+        for mb in args.sizes_mb:
+            n = int(mb * (1 << 20)) // 4
+            x = torch.randn(n, device="cuda") * 1e-2
+            reg = comm.register(x)
+            paths = [("ipc_push", lambda: comm.allreduce_registered_(reg, x, 1.0 / world))]
+            if nvls:
+                with torch.cuda.use_mem_pool(pool):
+                    xp = torch.empty(n, device="cuda")
+                xp.normal_().mul_(1e-2)
+                off = comm.nvls_offset(xp)
+                paths.append(("nvls_inplace", lambda: comm.allreduce_nvls_inplace_(off, n, 1.0 / world)))
+            iters = max(5, min(args.iters, int(1500 / max(mb, 1))))
+            shapes = [(b, p, u) for b in (48, 96, 128) for p in (2, 4, 8) for u in (0, 1, 2)] if not sumsq else [(-1, -1, -1)]
+            for path, fn in paths:
+                for (blocks, ppt, unroll) in shapes:
+                    if blocks > 0:
+                        comm.tune(blocks, ppt, unroll)
+                    ms = timed(fn, iters)
+                    if rank == 0:
+                        bus = n * 4 * 2 * (world - 1) / world / ms / 1e6
+                        emit(bench="allreduce_tune", world=world, size_mb=mb, path=path, max_blocks=blocks,
+                             packs_per_thread=ppt, unroll=unroll, sumsq=sumsq, us=ms * 1e3, bus_gbs=bus,
+                             frac_of_900=bus / 900.0)
+            comm.tune(int(os.environ.get("B2_AR_BLOCKS", "128")), int(os.environ.get("B2_AR_PACKS_PER_THREAD", "4")),
+                      int(os.environ.get("B2_AR_UNROLL", "0")))
+            comm.unregister(reg)
+            del x
+        comm.sumsq_clip_(1.0, torch.empty(2, device="cuda")) if sumsq else None
+    comm.enable_sumsq(False)
+    comm.check()
+    comm.close()
+    dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("bench", choices=["adamw", "ce", "ce_kernel", "lmce", "allreduce", "allreduce_emulated"])
+    ap.add_argument("bench", choices=["adamw", "ce", "ce_kernel", "lmce", "allreduce", "allreduce_emulated", "allreduce_tune"])
     ap.add_argument("--d-model", type=int, default=1024)
     ap.add_argument("--models", nargs="+", default=["t5-small", "flan-t5-base", "flan-t5-large", "flan-t5-xl"])
     ap.add_argument("--rows", nargs="+", type=int, default=[128, 1024, 8192, 32768])
@@ -415,7 +508,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--only", default="all", choices=["all", "ours"])
     args = ap.parse_args()
-    {"adamw": bench_adamw, "ce": bench_ce, "ce_kernel": bench_ce_kernel, "lmce": bench_lmce, "allreduce": bench_allreduce,
+    {"adamw": bench_adamw, "ce": bench_ce, "ce_kernel": bench_ce_kernel, "lmce": bench_lmce, "allreduce": bench_allreduce, "allreduce_tune": bench_allreduce_tune,
      "allreduce_emulated": bench_allreduce_emulated}[args.bench](args)
 
 

@@ -47,7 +47,8 @@ SIGNATURES = {
     "b2_ce_forward_noalloc": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _i32, _vp, _vp, _vp, _vp]),
     "b2_ce_backward": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _i32, _vp, _vp]),
     "b2_lmce_workspace_bytes": (_sz, [_i64, _i64]),
-    "b2_lmce_forward": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _i64, _i32, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "b2_lmce_forward": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _i64, _i32, _vp, _vp, _vp, _vp, _i64, _vp, _sz,
+                                  _vp]),
     "b2_lmce_backward_dlogits": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _i32, _vp, _i64,
                                            _vp]),
     "b2_adamw_plan": (_i64, [C.POINTER(AdamWTensor), C.c_int32]),
@@ -77,6 +78,7 @@ SIGNATURES = {
     "b2_allreduce_nvls_inplace": (C.c_int, [_vp, C.c_uint64, _i64, _f32, _vp]),
     "b2_comm_status": (C.c_int, [_vp]),
     "b2_comm_poll": (C.c_int, [_vp]),
+    "b2_comm_tune": (C.c_int, [_vp, _i32, _i32, _i32]),
     "b2_comm_status_word": (_vp, [_vp]),
     "b2_comm_sumsq_enable": (C.c_int, [_vp, _i32]),
     "b2_comm_sumsq_numel": (_i64, [_vp]),

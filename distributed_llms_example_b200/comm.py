@@ -269,6 +269,10 @@ class P2PComm:
         _lib.count_launch()
         return tensor
 
+    def tune(self, max_blocks: int = -1, packs_per_thread: int = -1, unroll: int = -1) -> None:
+        """Launch shape of the zero-copy kernels (same call on every rank; see b2_comm_tune)."""
+        _lib.check(self._lib.b2_comm_tune(self._ctx, max_blocks, packs_per_thread, unroll))
+
     def check(self) -> None:
         """Synchronising health check: raises if a kernel timed out waiting for a peer."""
         _lib.check(self._lib.b2_comm_status(self._ctx))

@@ -524,6 +524,7 @@ extern "C" int b2_comm_create(int rank, int world, size_t staging_bytes, b2_comm
   if (c->max_blocks < 1) c->max_blocks = 1;
   if (c->max_blocks > kArMaxBlocks) c->max_blocks = kArMaxBlocks;
   c->unroll = (int)env_ll("B2_AR_UNROLL", 0);
+  c->ppt = (int)env_ll("B2_AR_PACKS_PER_THREAD", 4);
   // A peer that has not arrived after this long is treated as dead (NCCL-watchdog scale: a
   // checkpoint save or an evaluation pass on one rank must not trip it).
   c->timeout_ns = (unsigned long long)env_ll("B2_AR_TIMEOUT_MS", 600000) * 1000000ull;
@@ -607,7 +608,7 @@ extern "C" int b2_allreduce(b2_comm* c, void* buf, int64_t numel, int wire_dtype
     }
     KernelFn fn = pick_kernel<1>(c->world, bf16w, a);
     if (!fn) return fail(B2_ERR_INVALID, "allreduce: no kernel for world %d", c->world);
-    const int nb = pick_blocks(n / epp, c->max_blocks);
+    const int nb = pick_blocks(n / epp, c->max_blocks, c->ppt);
     long long n_arg = n;
     float scale_arg = scale;
     uint32_t epoch = c->epoch;
@@ -731,7 +732,7 @@ extern "C" int b2_allreduce_registered(b2_comm* c, int reg_id, int64_t numel, fl
   static const bool pull = env_ll("B2_AR_ZERO_COPY_PULL", 0) != 0;  // A/B knob: two-shot pull variant
   KernelFn fn = pull ? pick_inplace_kernel<1>(c->world) : pick_push_kernel<1>(c->world);
   if (!fn) return fail(B2_ERR_INVALID, "allreduce_registered: no kernel for world %d", c->world);
-  const int nb = pick_blocks(numel / 4 / c->world, c->max_blocks);
+  const int nb = pick_blocks(numel / 4 / c->world, c->max_blocks, c->ppt);
   long long n_arg = numel;
   float scale_arg = scale;
   uint32_t epoch = c->epoch;
@@ -785,6 +786,18 @@ extern "C" int b2_comm_status(b2_comm* c) {
   uint32_t s = 0;
   B2_CUDA_CHECK(cudaMemcpy(&s, c->base[c->rank] + kStatusOff, 4, cudaMemcpyDeviceToHost));
   if (s != 0 || *(volatile uint32_t*)c->host_status != 0) return timeout_error(c);
+  return B2_OK;
+}
+
+// Launch-shape knobs of the zero-copy kernels, settable at run time so that one process can sweep
+// them (benchmarks/microbench.py allreduce_tune); negative values leave a knob unchanged. All
+// ranks must make the same call at the same point of their call sequence.
+extern "C" int b2_comm_tune(b2_comm* c, int max_blocks, int packs_per_thread, int unroll) {
+  using namespace b2;
+  B2_REQUIRE(c, "comm_tune: null comm");
+  if (max_blocks > 0) c->max_blocks = max_blocks > kArMaxBlocks ? kArMaxBlocks : max_blocks;
+  if (packs_per_thread > 0) c->ppt = packs_per_thread;
+  if (unroll >= 0) c->unroll = unroll;
   return B2_OK;
 }
 

@@ -283,11 +283,11 @@ static inline long long env_ll(const char* name, long long dflt) {
 
 // One-shot moves (W-1)*S inbound per rank and needs one barrier; two-shot moves
 // 2(W-1)/W*S and needs two. At W=2 the bytes are equal, so one-shot always wins.
-static inline int pick_blocks(long long npack, int max_blocks) {
-  // B2_AR_PACKS_PER_THREAD 16-byte packs per thread before adding a CTA (default 4: a 25 MiB
-  // bucket at world 8 fills ~100 CTAs); small buckets stay on few CTAs so the barrier is cheap
-  // and the backward GEMMs keep their SMs.
-  static const long long ppt = []{ long long v = env_ll("B2_AR_PACKS_PER_THREAD", 4); return v < 1 ? 1 : v; }();
+static inline int pick_blocks(long long npack, int max_blocks, long long packs_per_thread = 4) {
+  // `packs_per_thread` 16-byte packs per thread before adding a CTA (B2_AR_PACKS_PER_THREAD,
+  // default 4: a 25 MiB bucket at world 8 fills ~100 CTAs); small buckets stay on few CTAs so the
+  // barrier is cheap and the backward GEMMs keep their SMs.
+  const long long ppt = packs_per_thread < 1 ? 1 : packs_per_thread;
   long long nb = (npack + (long long)kArThreads * ppt - 1) / ((long long)kArThreads * ppt);
   if (nb < 1) nb = 1;
   if (nb > max_blocks) nb = max_blocks;
@@ -328,6 +328,7 @@ struct b2_comm {
   int parity = 0;
   int max_blocks = 128;
   int unroll = 0;                       // B2_AR_UNROLL: loads-in-flight variant of the zero-copy kernels
+  int ppt = 4;                          // B2_AR_PACKS_PER_THREAD: 16-byte packs per thread before adding a CTA
   unsigned long long timeout_ns = 600ull * 1000000000ull;
   uint32_t* host_status = nullptr;      // mapped pinned host word the kernels mirror the status into
   uint32_t* host_status_dev = nullptr;  // its device-side address

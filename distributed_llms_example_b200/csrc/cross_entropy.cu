@@ -144,10 +144,30 @@ __device__ __forceinline__ float packs_max(const uint4 (&r)[U]) {
   }
 }
 
+// 2^x for x <= 0 on the FMA and integer pipes only (no MUFU): round-to-nearest split x = n + f with
+// the 1.5*2^23 trick, a degree-4 polynomial for 2^f on [-0.5, 0.5] (max relative error 3.7e-6,
+// far inside the 1e-5 bar of the parity tests), then n added into the exponent field. One element
+// in four of the bf16 forward goes this way: with one MUFU.EX2 per element the XU pipe (16/clk/SM)
+// caps the kernel near 6 TB/s of bf16 logits, below what HBM delivers (ncu: pipe_xu 72 % busy at
+// 4.4 TB/s); with a quarter of the exponentials moved over, XU and FMA pipes are balanced above
+// the HBM rate. x < -126 gives 0; NaN propagates like the MUFU path.
+__device__ __forceinline__ float poly_exp2(float x) {
+  const float kMagic = 12582912.f;  // 1.5 * 2^23
+  const float t = __fadd_rn(x, kMagic);
+  const float n = __fsub_rn(t, kMagic);
+  const float f = __fsub_rn(x, n);
+  float p = __fmaf_rn(0.009676037356257439f, f, 0.05592203512787819f);
+  p = __fmaf_rn(p, f, 0.2402210682630539f);
+  p = __fmaf_rn(p, f, 0.6931210160255432f);
+  p = __fmaf_rn(p, f, 1.0000001192092896f);
+  const float r = __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
+  return x < -126.f ? 0.f : r;
+}
+
 // st <- st merged with the U packs in r: one FFMA + one MUFU.EX2 + one FADD per element.
 // exp(x - ref) is evaluated as ex2(x*log2e - ref*log2e); NaN inputs propagate (hmax2/fmaxf drop
 // NaN from the max, but ex2(NaN) lands in the sum).
-template <bool BF16, int U>
+template <bool BF16, int U, bool POLY = false>
 __device__ __forceinline__ void ms_update_packs(MS& st, const uint4 (&r)[U]) {
   using E = Elem<BF16>;
   const float m = fmaxf(st.m, packs_max<BF16, U>(r));
@@ -161,7 +181,10 @@ __device__ __forceinline__ void ms_update_packs(MS& st, const uint4 (&r)[U]) {
 #pragma unroll
     for (int k = 0; k < E::kPerPack; k += 2) {
       acc0 += fast_exp2(fmaf(x[k], kLog2e, neg));
-      acc1 += fast_exp2(fmaf(x[k + 1], kLog2e, neg));
+      if (POLY && (k & 2))  // elements 3 and 7 of every pack of 8 take the FMA-pipe polynomial
+        acc1 += poly_exp2(fmaf(x[k + 1], kLog2e, neg));
+      else
+        acc1 += fast_exp2(fmaf(x[k + 1], kLog2e, neg));
     }
   }
   st.s = st.s * fast_exp2(fmaf(st.m, kLog2e, neg)) + (acc0 + acc1);
@@ -182,12 +205,69 @@ __device__ __forceinline__ MS warp_merge(MS st) {
   return st;
 }
 
+// The tail of ce_forward_kernel, run by the last CTA to arrive. Kept out of line so that its
+// registers (a batch of rows and all partials of a row in flight) do not raise the pressure in the
+// streaming loop, which is compiled for 4 CTAs per SM.
+__device__ __noinline__ void ce_fold_rows(const CeScratch sc, const long long* __restrict__ labels,
+                                          long long n_rows, int vocab, long long ignore_index, int split,
+                                          float* __restrict__ row_lse, float* acc_out, float* cnt_out) {
+  // Last CTA to arrive: (split rows only) fold the partials of each row, then sum the valid
+  // rows' losses in a fixed order (thread-strided, then a tree), so the result does not
+  // depend on which CTA happened to be last. Everything read here is coalesced, and the loads
+  // of kFoldRows rows (and of all partials of a row) are issued before the first one is used:
+  // written as a plain loop this tail cost one L2 round trip per row per thread, ~20-30 us of a
+  // 35-120 us kernel (N <= 8192); batched it is a handful of round trips.
+  constexpr int kFoldRows = 8;
+  float acc = 0.f, cnt = 0.f;
+  for (long long r0 = threadIdx.x; r0 < n_rows; r0 += (long long)kCeThreads * kFoldRows) {
+    long long ys[kFoldRows];
+    float ls[kFoldRows];
+#pragma unroll
+    for (int i = 0; i < kFoldRows; ++i) {
+      const long long r = r0 + (long long)i * kCeThreads;
+      ys[i] = ignore_index;
+      ls[i] = 0.f;
+      if (r < n_rows) {
+        ys[i] = labels[r];
+        ls[i] = __ldcg(sc.row_loss + r);
+      }
+    }
+    if (split != 1) {
+#pragma unroll 2
+      for (int i = 0; i < kFoldRows; ++i) {
+        const long long r = r0 + (long long)i * kCeThreads;
+        if (r >= n_rows) break;
+        float2 q[kCeMaxSplit];
+#pragma unroll
+        for (int k = 0; k < kCeMaxSplit; ++k)
+          if (k < split) q[k] = __ldcg(reinterpret_cast<const float2*>(sc.partial + r * split + k));
+        MS t{-INFINITY, 0.f};
+#pragma unroll
+        for (int k = 0; k < kCeMaxSplit; ++k)
+          if (k < split) t = ms_merge(t, MS{q[k].x, q[k].y});
+        const float lse = t.m + logf(t.s);
+        row_lse[r] = lse;
+        ls[i] = (ys[i] < 0 || ys[i] >= vocab) ? __int_as_float(0x7fc00000) : lse - ls[i];
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < kFoldRows; ++i) {  // same rows, same order as a plain strided loop
+      if (ys[i] != ignore_index) {
+        acc += ls[i];
+        cnt += 1.f;
+      }
+    }
+  }
+  *acc_out = acc;
+  *cnt_out = cnt;
+}
+
 // The unit of work is a WARP, not a CTA: warp w of the grid walks work items (row, part) with
 // stride (gridDim.x * 8). A warp streams its piece with 512-byte coalesced requests, merges with
 // shuffles only and never waits for another warp, so there is no CTA barrier on the data path
 // (an earlier CTA-per-row version spent as many issue slots stalled on bar.sync as on memory).
 // Loads for the next batch of packs are issued before the current batch is reduced.
-template <bool BF16>
+template <bool BF16, bool POLY>
 __global__ void __launch_bounds__(kCeThreads, kCeFwdCtasPerSM)
 ce_forward_kernel(const typename Elem<BF16>::T* __restrict__ logits,
                   const long long* __restrict__ labels, long long n_rows, int vocab,
@@ -237,15 +317,15 @@ ce_forward_kernel(const typename Elem<BF16>::T* __restrict__ logits,
         uint4 nxt[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) nxt[u] = ld_nc16(zp + i + u * 32);
-        ms_update_packs<BF16, U>(st, cur);
+        ms_update_packs<BF16, U, POLY>(st, cur);
 #pragma unroll
         for (int u = 0; u < U; ++u) cur[u] = nxt[u];
       }
-      ms_update_packs<BF16, U>(st, cur);
+      ms_update_packs<BF16, U, POLY>(st, cur);
     }
     for (; i < p1; i += 32) {
       const uint4 one[1] = {ld_nc16(zp + i)};
-      ms_update_packs<BF16, 1>(st, one);
+      ms_update_packs<BF16, 1, POLY>(st, one);
     }
     // Scalar tail (vocab % PP, or the whole row if it is not 16-byte aligned): last part only.
     if (part == split - 1) {
@@ -282,29 +362,8 @@ ce_forward_kernel(const typename Elem<BF16>::T* __restrict__ logits,
   if (!s_last) return;
   __threadfence();
 
-  // Last CTA to arrive: (split rows only) fold the partials of each row, then sum the valid
-  // rows' losses in a fixed order (thread-strided, then a tree), so the result does not
-  // depend on which CTA happened to be last. Everything read here is coalesced.
-  float acc = 0.f, cnt = 0.f;
-  for (long long r = threadIdx.x; r < n_rows; r += kCeThreads) {
-    const long long y = labels[r];
-    const bool valid = (y != ignore_index);
-    float l = __ldcg(sc.row_loss + r);
-    if (split != 1) {
-      MS t{-INFINITY, 0.f};
-      for (int k = 0; k < split; ++k) {
-        const float2 q = __ldcg(reinterpret_cast<const float2*>(sc.partial + r * split + k));
-        t = ms_merge(t, MS{q.x, q.y});
-      }
-      const float lse = t.m + logf(t.s);
-      row_lse[r] = lse;
-      l = (y < 0 || y >= vocab) ? __int_as_float(0x7fc00000) : lse - l;
-    }
-    if (valid) {
-      acc += l;
-      cnt += 1.f;
-    }
-  }
+  float acc, cnt;
+  ce_fold_rows(sc, labels, n_rows, vocab, ignore_index, split, row_lse, &acc, &cnt);
   acc = block_sum(acc, s_f);
   cnt = block_sum(cnt, s_f);
   if (threadIdx.x == 0) {
@@ -394,6 +453,14 @@ ce_backward_kernel(const typename Elem<BF16>::T* __restrict__ logits,
 }
 
 // CTAs per SM the persistent grids are capped at; 0 = one CTA per work item (no cap).
+// B2_CE_POLY=1 moves a quarter of the bf16 forward's exponentials from MUFU.EX2 to poly_exp2 (read
+// on every call so that a benchmark can A/B the two in one process). Default off: see
+// profiles/README.md for the measured A/B.
+static bool ce_poly() {
+  const char* s = std::getenv("B2_CE_POLY");
+  return s && s[0] == '1';
+}
+
 // B2_CE_FWD_CTAS_PER_SM / B2_CE_BWD_CTAS_PER_SM override the defaults for tuning runs.
 static int env_int(const char* name, int dflt) {
   const char* v = std::getenv(name);
@@ -454,12 +521,16 @@ extern "C" int b2_ce_forward(const void* logits, const int64_t* labels, int64_t 
   B2_REQUIRE((((uintptr_t)workspace) & 15) == 0, "ce_forward: workspace must be 16-byte aligned");
   const int split = pick_split(n_rows);
   const long long grid = fwd_grid(n_rows * split);
-  if (dtype == B2_BF16) {
-    ce_forward_kernel<true><<<(unsigned)grid, kCeThreads, 0, (cudaStream_t)stream>>>(
+  if (dtype == B2_BF16 && ce_poly()) {
+    ce_forward_kernel<true, true><<<(unsigned)grid, kCeThreads, 0, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)logits, (const long long*)labels, n_rows, (int)vocab, row_stride,
+        ignore_index, split, row_lse, loss_out, nvalid_out, workspace);
+  } else if (dtype == B2_BF16) {
+    ce_forward_kernel<true, false><<<(unsigned)grid, kCeThreads, 0, (cudaStream_t)stream>>>(
         (const __nv_bfloat16*)logits, (const long long*)labels, n_rows, (int)vocab, row_stride,
         ignore_index, split, row_lse, loss_out, nvalid_out, workspace);
   } else {
-    ce_forward_kernel<false><<<(unsigned)grid, kCeThreads, 0, (cudaStream_t)stream>>>(
+    ce_forward_kernel<false, false><<<(unsigned)grid, kCeThreads, 0, (cudaStream_t)stream>>>(
         (const float*)logits, (const long long*)labels, n_rows, (int)vocab, row_stride,
         ignore_index, split, row_lse, loss_out, nvalid_out, workspace);
   }
@@ -580,12 +651,16 @@ extern "C" int b2_ce_forward_noalloc(const void* logits, const int64_t* labels, 
   B2_CUDA_CHECK(cudaMemsetAsync(ws, 0, 16, st));
   const int split = pick_split(n_rows);
   const long long grid = fwd_grid(n_rows * split);
-  if (dtype == B2_BF16) {
-    ce_forward_kernel<true><<<(unsigned)grid, kCeThreads, 0, st>>>(
+  if (dtype == B2_BF16 && ce_poly()) {
+    ce_forward_kernel<true, true><<<(unsigned)grid, kCeThreads, 0, st>>>(
+        (const __nv_bfloat16*)logits, (const long long*)labels, n_rows, (int)vocab, row_stride,
+        ignore_index, split, row_lse, loss_out, nvalid_out, ws);
+  } else if (dtype == B2_BF16) {
+    ce_forward_kernel<true, false><<<(unsigned)grid, kCeThreads, 0, st>>>(
         (const __nv_bfloat16*)logits, (const long long*)labels, n_rows, (int)vocab, row_stride,
         ignore_index, split, row_lse, loss_out, nvalid_out, ws);
   } else {
-    ce_forward_kernel<false><<<(unsigned)grid, kCeThreads, 0, st>>>(
+    ce_forward_kernel<false, false><<<(unsigned)grid, kCeThreads, 0, st>>>(
         (const float*)logits, (const long long*)labels, n_rows, (int)vocab, row_stride,
         ignore_index, split, row_lse, loss_out, nvalid_out, ws);
   }

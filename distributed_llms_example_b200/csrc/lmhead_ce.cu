@@ -23,11 +23,16 @@
 // one (max, sum) partial per row; lmce_finish_kernel merges the partials per row in split order
 // and reduces the loss with a fixed-order last-block sum (deterministic).
 //
-// Backward: the same main loop recomputes the logits tile, the epilogue turns it into
-//     dlogits = (exp(z - lse) - [j == y]) * g / n_valid      (0 on ignored rows)
-// in bf16 and writes it once; dX = dlogits @ W and dW = dlogits^T @ X are plain library GEMMs in
-// the Python adapter. (Chaining dlogits into two more tcgen05 contractions without the HBM round
-// trip is the next step; see DESIGN.md.)
+// Two more epilogues share the main loop:
+//   forward + store   the bf16 logits are ALSO written, once, on their way out of TMEM (registers ->
+//                     128B-swizzled shared memory -> cp.async.bulk.tensor store), so the forward
+//                     never re-reads them and the backward can be the HBM-bound b2_ce_backward.
+//                     This is the fastest pairing on B200: re-reading 2 bytes per logit costs less
+//                     than recomputing 2*d_model flop per logit (measured, profiles/README.md).
+//   dlogits           the logits tile is recomputed and the epilogue writes
+//                       dlogits = (exp(z - lse) - [j == y]) * g / n_valid      (0 on ignored rows)
+//                     in bf16: no [N, V] tensor is kept between forward and backward (memory-lean).
+// dX = dlogits @ W and dW = dlogits^T @ X are plain library GEMMs in the Python adapter.
 //
 // Numerics: fp32 accumulation over K; with round_bf16 != 0 each logit is rounded to bf16 before
 // the softmax, which is exactly what the unfused path computes from its bf16 logits tensor.
@@ -50,8 +55,10 @@ constexpr int kStageBytes = kABytes + kBBytes;
 constexpr int kThreads = 192;    // warp 0 TMA, warp 1 MMA, warps 2-5 epilogue
 constexpr int kTmemCols = 512;
 constexpr int kMaxSplits = 64;
-// shared memory: [stages x (A | B)] then barriers, 1024-byte aligned for the 128B swizzle
-constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*alignment slack*/ + 256 /*barriers*/;
+constexpr int kGroup = 64;                 // columns per epilogue step: 64 bf16 = one 128-byte swizzle row
+constexpr int kOutBytes = 32 * kGroup * 2; // per epilogue warp: 32 rows x 128 bytes staged for the TMA store
+// shared memory: [stages x (A | B)] [4 x store staging] then barriers, 1024-byte aligned for the 128B swizzle
+constexpr int kSmemBytes = kStages * kStageBytes + 4 * kOutBytes + 1024 /*alignment slack*/ + 256 /*barriers*/;
 
 // ---- PTX wrappers ------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -86,6 +93,16 @@ __device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint64_t* ba
       ::"r"(smem_u32(dst)), "l"((uint64_t)map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
       : "memory");
 }
+// shared -> global tile store; rows / columns outside the tensor are clipped by the hardware
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, const void* src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"((uint64_t)map),
+               "r"(smem_u32(src)), "r"(c0), "r"(c1)
+               : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
   asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)map) : "memory");
 }
@@ -167,30 +184,32 @@ struct Params {
   const float* row_lse;  // [n_rows], natural log
   const float* grad_out; // device scalar
   const float* nvalid;   // device scalar
-  __nv_bfloat16* dlogits;
-  long long ld;          // dlogits row pitch in elements
 };
 
 __device__ __forceinline__ float round_to_bf16(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
 
-// One CTA = one (row block, split). MODE 0: forward (online LSE), MODE 1: backward (dlogits).
+// One CTA = one (row block, split). MODE 0: forward (online LSE); MODE 1: backward (recompute,
+// write dlogits); MODE 2: forward that also writes the bf16 logits.
 template <int MODE>
 __global__ void __launch_bounds__(kThreads, 1)
 lmce_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
-            const __grid_constant__ Params p) {
+            const __grid_constant__ CUtensorMap map_out, const __grid_constant__ Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  Barriers* bars = (Barriers*)(smem + kStages * kStageBytes);
+  uint8_t* out_stage = smem + kStages * kStageBytes;
+  Barriers* bars = (Barriers*)(out_stage + 4 * kOutBytes);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int rb = blockIdx.x / p.splits, split = blockIdx.x % p.splits;
   const int t_begin = split * p.tiles_per_split;
   const int t_end = min(t_begin + p.tiles_per_split, p.n_vtiles);
   const int n_tiles = max(t_end - t_begin, 0);
   const int n_kb = (int)(p.d_model / kBK);
+  constexpr bool kStore = (MODE != 0);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&map_x);
     tma_prefetch_desc(&map_w);
+    if (kStore) tma_prefetch_desc(&map_out);
     for (int i = 0; i < kStages; ++i) {
       mbar_init(&bars->full[i], 1);
       mbar_init(&bars->empty[i], 1);
@@ -260,11 +279,12 @@ lmce_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ C
     const bool valid = row_ok && label != p.ignore_index;
     float m = -INFINITY, s = 0.f, zl = 0.f;
     bool have_label = false;
-    float lse2 = 0.f, coef = 0.f;
+    float nlse2 = 0.f, coef = 0.f;
     if (MODE == 1) {
-      lse2 = row_ok ? p.row_lse[row] * kLog2e : 0.f;
+      nlse2 = row_ok ? -p.row_lse[row] * kLog2e : 0.f;
       coef = valid ? p.grad_out[0] / p.nvalid[0] : 0.f;
     }
+    uint8_t* my_stage = out_stage + q * kOutBytes;   // 32 rows x 128 B, 128B-swizzled like the TMA box
     for (int t = 0; t < n_tiles; ++t) {
       const int acc = t & 1;
       const uint32_t acc_phase = (uint32_t)(t >> 1) & 1;
@@ -274,61 +294,84 @@ lmce_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ C
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * kBN);
       const long long lc = valid ? label - col0 : -1;   // label's column inside this tile, if any
 #pragma unroll 1
-      for (int c = 0; c < kBN / 32; ++c) {
-        const long long cbase = col0 + c * 32;
-        if (cbase >= p.vocab) break;                    // whole chunk beyond the vocabulary (last tile)
-        uint32_t v[32];
-        tmem_ld32(taddr + (uint32_t)(c * 32), v);
+      for (int gi = 0; gi < kBN / kGroup; ++gi) {
+        const long long cbase = col0 + gi * kGroup;
+        if (cbase >= p.vocab) break;                    // whole group beyond the vocabulary (last tile)
+        uint32_t v[kGroup];
+        tmem_ld32(taddr + (uint32_t)(gi * kGroup), v);
+        tmem_ld32(taddr + (uint32_t)(gi * kGroup + 32), v + 32);
         tmem_ld_wait();
-        float z[32];
+        float z[kGroup];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
+        for (int j = 0; j < kGroup; ++j) {
           z[j] = __uint_as_float(v[j]);
           if (p.round_bf16) z[j] = round_to_bf16(z[j]);
         }
-        const int ncol = (int)min((long long)32, p.vocab - cbase);  // < 32 only in the last chunk
-        if (MODE == 0) {
-          if (lc >= c * 32 && lc < c * 32 + 32) {
-            const int jl = (int)(lc - c * 32);
+        const int ncol = (int)min((long long)kGroup, p.vocab - cbase);  // < 64 only in the last group
+        const bool label_here = lc >= gi * kGroup && lc < gi * kGroup + kGroup;
+        const int jl = (int)(lc - gi * kGroup);
+        uint32_t o[kGroup / 2];
+        if (MODE == 2) {
+          if (ncol < kGroup) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
+            for (int j = 0; j < kGroup; ++j)
+              if (j >= ncol) z[j] = 0.f;   // padding columns of the last group are stored as zeros
+          }
+#pragma unroll
+          for (int j = 0; j < kGroup; j += 2) o[j >> 1] = pack_bf16(z[j], z[j + 1]);
+        }
+        if (MODE != 1) {
+          if (label_here) {
+#pragma unroll
+            for (int j = 0; j < kGroup; ++j)
               if (j == jl) zl = z[j];
             have_label = true;
           }
           float cm = -INFINITY;
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
+          for (int j = 0; j < kGroup; ++j) {
             z[j] = (j < ncol) ? z[j] * kLog2e : -INFINITY;
             cm = fmaxf(cm, z[j]);
           }
           const float mn = fmaxf(m, cm);
-          float add = 0.f;
+          float add0 = 0.f, add1 = 0.f;
 #pragma unroll
-          for (int j = 0; j < 32; ++j) add += fast_exp2(z[j] - mn);
-          s = s * fast_exp2(m - mn) + add;
+          for (int j = 0; j < kGroup; j += 2) {
+            add0 += fast_exp2(z[j] - mn);
+            add1 += fast_exp2(z[j + 1] - mn);
+          }
+          s = s * fast_exp2(m - mn) + (add0 + add1);
           m = mn;
         } else {
-          // dlogits = (softmax - onehot) * g / n_valid, bf16, 64 contiguous bytes per thread per chunk
-          uint32_t o[16];
+          // dlogits = (softmax - onehot) * g / n_valid
 #pragma unroll
-          for (int j = 0; j < 32; j += 2) {
-            float d0 = fast_exp2(__fmaf_rn(z[j], kLog2e, -lse2)) * coef;
-            float d1 = fast_exp2(__fmaf_rn(z[j + 1], kLog2e, -lse2)) * coef;
-            if (lc == c * 32 + j) d0 -= coef;
-            if (lc == c * 32 + j + 1) d1 -= coef;
-            o[j >> 1] = pack_bf16(d0, d1);
-          }
-          if (row_ok) {
-            __nv_bfloat16* dst = p.dlogits + row * p.ld + cbase;
-            if (ncol == 32) {
+          for (int j = 0; j < kGroup; ++j) z[j] = fast_exp2(__fmaf_rn(z[j], kLog2e, nlse2)) * coef;
+          if (label_here) {
 #pragma unroll
-              for (int i = 0; i < 4; ++i)
-                st_stream16(dst + i * 8, make_uint4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]));
-            } else {
-              for (int j = 0; j < ncol; ++j)
-                dst[j] = __ushort_as_bfloat16((unsigned short)((j & 1) ? (o[j >> 1] >> 16) : (o[j >> 1] & 0xffffu)));
-            }
+            for (int j = 0; j < kGroup; ++j)
+              if (j == jl) z[j] -= coef;
           }
+          if (ncol < kGroup) {
+#pragma unroll
+            for (int j = 0; j < kGroup; ++j)
+              if (j >= ncol) z[j] = 0.f;
+          }
+#pragma unroll
+          for (int j = 0; j < kGroup; j += 2) o[j >> 1] = pack_bf16(z[j], z[j + 1]);
+        }
+        if (kStore) {
+          // registers -> swizzled shared memory -> one TMA store of [32 rows x 64 columns] per warp.
+          // The previous store must have finished READING the staging tile before it is overwritten.
+          if (lane == 0) tma_store_wait_read();
+          __syncwarp();
+          uint8_t* rowp = my_stage + lane * 128;
+#pragma unroll
+          for (int c16 = 0; c16 < 8; ++c16)
+            *reinterpret_cast<uint4*>(rowp + ((c16 ^ (lane & 7)) << 4)) =
+                make_uint4(o[4 * c16], o[4 * c16 + 1], o[4 * c16 + 2], o[4 * c16 + 3]);
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) tma_store_2d(&map_out, my_stage, (int)cbase, (int)((long long)rb * kBM + q * 32));
         }
       }
       // this accumulator may be overwritten by the MMA of tile t+2
@@ -336,10 +379,11 @@ lmce_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ C
       __syncwarp();
       if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
     }
-    if (MODE == 0 && row_ok) {
+    if (MODE != 1 && row_ok) {
       p.partial[row * p.splits + split] = make_float2(m, s);
       if (have_label) p.zlabel[row] = zl;
     }
+    if (kStore && lane == 0) tma_store_wait_all();   // bulk stores complete before the CTA may exit
   }
   tc_fence_before();
   __syncthreads();
@@ -442,6 +486,23 @@ static int make_map(CUtensorMap* map, const void* base, long long rows, long lon
   return B2_OK;
 }
 
+// [rows, vocab] bf16 output with row pitch ld: boxes of [32 rows, 64 columns], 128-byte swizzle
+static int make_out_map(CUtensorMap* map, void* base, long long rows, long long vocab, long long ld) {
+  EncodeTiled enc;
+  int rc = encode_fn(&enc);
+  if (rc != B2_OK) return rc;
+  // stores move whole 16-byte units: the columns [vocab, vocab rounded up to 8) receive zeros
+  const cuuint64_t dims[2] = {(cuuint64_t)((vocab + 7) / 8 * 8), (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  const cuuint32_t box[2] = {(cuuint32_t)kGroup, 32};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(B2_ERR_CUDA, "lmce: cuTensorMapEncodeTiled (output) failed with CUresult %d", (int)r);
+  return B2_OK;
+}
+
 // splits per row block: fewest (waves x tiles per CTA), ties to the smaller partial array
 static int pick_splits(long long row_blocks, int n_vtiles) {
   long long best_cost = -1;
@@ -484,21 +545,10 @@ extern "C" size_t b2_lmce_workspace_bytes(int64_t n_rows, int64_t vocab) {
   return 16 + (size_t)n_rows * kMaxSplits * 8 + (size_t)n_rows * 4 + (size_t)blocks * 8 + 64;
 }
 
-extern "C" int b2_lmce_forward(const void* hidden, const void* weight, const int64_t* labels, int64_t n_rows,
-                               int64_t vocab, int64_t d_model, int64_t ignore_index, int round_bf16,
-                               float* row_lse, float* loss_out, float* nvalid_out, void* workspace,
-                               size_t workspace_bytes, b2_stream_t stream) {
-  using namespace b2;
+static int fill_params(b2::lmce::Params& p, const int64_t* labels, int64_t n_rows, int64_t vocab, int64_t d_model,
+                       int64_t ignore_index, int round_bf16) {
   using namespace b2::lmce;
-  int rc = check_common(hidden, weight, (const long long*)labels, n_rows, vocab, d_model);
-  if (rc != B2_OK) return rc;
-  B2_REQUIRE(row_lse && loss_out && nvalid_out && workspace, "lmce_forward: null pointer");
-  B2_REQUIRE(workspace_bytes >= b2_lmce_workspace_bytes(n_rows, vocab) && (((uintptr_t)workspace) & 15) == 0,
-             "lmce_forward: workspace too small or not 16-byte aligned");
-  CUtensorMap map_x, map_w;
-  if ((rc = make_map(&map_x, hidden, n_rows, d_model, kBM)) != B2_OK) return rc;
-  if ((rc = make_map(&map_w, weight, vocab, d_model, kBN)) != B2_OK) return rc;
-  Params p = {};
+  p = Params{};
   p.labels = (const long long*)labels;
   p.n_rows = n_rows; p.vocab = vocab; p.d_model = d_model; p.ignore_index = ignore_index;
   p.n_vtiles = (int)((vocab + kBN - 1) / kBN);
@@ -507,6 +557,33 @@ extern "C" int b2_lmce_forward(const void* hidden, const void* weight, const int
   p.tiles_per_split = (p.n_vtiles + p.splits - 1) / p.splits;
   p.splits = (p.n_vtiles + p.tiles_per_split - 1) / p.tiles_per_split;  // no empty trailing split
   p.round_bf16 = round_bf16;
+  return (int)(row_blocks * p.splits);
+}
+
+extern "C" int b2_lmce_forward(const void* hidden, const void* weight, const int64_t* labels, int64_t n_rows,
+                               int64_t vocab, int64_t d_model, int64_t ignore_index, int round_bf16,
+                               float* row_lse, float* loss_out, float* nvalid_out, void* logits_out,
+                               int64_t logits_stride, void* workspace, size_t workspace_bytes,
+                               b2_stream_t stream) {
+  using namespace b2;
+  using namespace b2::lmce;
+  int rc = check_common(hidden, weight, (const long long*)labels, n_rows, vocab, d_model);
+  if (rc != B2_OK) return rc;
+  B2_REQUIRE(row_lse && loss_out && nvalid_out && workspace, "lmce_forward: null pointer");
+  B2_REQUIRE(workspace_bytes >= b2_lmce_workspace_bytes(n_rows, vocab) && (((uintptr_t)workspace) & 15) == 0,
+             "lmce_forward: workspace too small or not 16-byte aligned");
+  B2_REQUIRE(!logits_out || (logits_stride >= vocab && logits_stride % 8 == 0 && (((uintptr_t)logits_out) & 15) == 0),
+             "lmce_forward: logits_out needs a 16-byte aligned base and a row pitch >= vocab that is a multiple of 8");
+  CUtensorMap map_x, map_w, map_out;
+  if ((rc = make_map(&map_x, hidden, n_rows, d_model, kBM)) != B2_OK) return rc;
+  if ((rc = make_map(&map_w, weight, vocab, d_model, kBN)) != B2_OK) return rc;
+  if (logits_out) {
+    if ((rc = make_out_map(&map_out, logits_out, n_rows, vocab, logits_stride)) != B2_OK) return rc;
+  } else {
+    map_out = map_x;  // unused by the kernel variant launched below
+  }
+  Params p;
+  const int grid = fill_params(p, labels, n_rows, vocab, d_model, ignore_index, round_bf16);
   char* ws = (char*)workspace;
   unsigned int* counter = (unsigned int*)ws;
   p.partial = (float2*)(ws + 16);
@@ -515,9 +592,13 @@ extern "C" int b2_lmce_forward(const void* hidden, const void* weight, const int
   static bool attr_done = false;
   if (!attr_done) {
     if ((rc = set_smem_attr((const void*)lmce_kernel<0>)) != B2_OK) return rc;
+    if ((rc = set_smem_attr((const void*)lmce_kernel<2>)) != B2_OK) return rc;
     attr_done = true;
   }
-  lmce_kernel<0><<<(unsigned)(row_blocks * p.splits), kThreads, kSmemBytes, (cudaStream_t)stream>>>(map_x, map_w, p);
+  if (logits_out)
+    lmce_kernel<2><<<(unsigned)grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(map_x, map_w, map_out, p);
+  else
+    lmce_kernel<0><<<(unsigned)grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(map_x, map_w, map_out, p);
   B2_CUDA_CHECK(cudaGetLastError());
   const unsigned fin_blocks = (unsigned)((n_rows + kFinThreads - 1) / kFinThreads);
   lmce_finish_kernel<<<fin_blocks, kFinThreads, 0, (cudaStream_t)stream>>>(
@@ -538,27 +619,19 @@ extern "C" int b2_lmce_backward_dlogits(const void* hidden, const void* weight, 
   B2_REQUIRE(row_lse && grad_out && nvalid && dlogits, "lmce_backward: null pointer");
   B2_REQUIRE(row_stride >= vocab && row_stride % 8 == 0 && (((uintptr_t)dlogits) & 15) == 0,
              "lmce_backward: dlogits needs a 16-byte aligned base and a row pitch >= vocab that is a multiple of 8");
-  CUtensorMap map_x, map_w;
+  CUtensorMap map_x, map_w, map_out;
   if ((rc = make_map(&map_x, hidden, n_rows, d_model, kBM)) != B2_OK) return rc;
   if ((rc = make_map(&map_w, weight, vocab, d_model, kBN)) != B2_OK) return rc;
-  Params p = {};
-  p.labels = (const long long*)labels;
-  p.n_rows = n_rows; p.vocab = vocab; p.d_model = d_model; p.ignore_index = ignore_index;
-  p.n_vtiles = (int)((vocab + kBN - 1) / kBN);
-  const long long row_blocks = (n_rows + kBM - 1) / kBM;
-  p.splits = pick_splits(row_blocks, p.n_vtiles);
-  p.tiles_per_split = (p.n_vtiles + p.splits - 1) / p.splits;
-  p.splits = (p.n_vtiles + p.tiles_per_split - 1) / p.tiles_per_split;
-  p.round_bf16 = round_bf16;
+  if ((rc = make_out_map(&map_out, dlogits, n_rows, vocab, row_stride)) != B2_OK) return rc;
+  Params p;
+  const int grid = fill_params(p, labels, n_rows, vocab, d_model, ignore_index, round_bf16);
   p.row_lse = row_lse; p.grad_out = grad_out; p.nvalid = nvalid;
-  p.dlogits = (__nv_bfloat16*)dlogits;
-  p.ld = row_stride;
   static bool attr_done = false;
   if (!attr_done) {
     if ((rc = set_smem_attr((const void*)lmce_kernel<1>)) != B2_OK) return rc;
     attr_done = true;
   }
-  lmce_kernel<1><<<(unsigned)(row_blocks * p.splits), kThreads, kSmemBytes, (cudaStream_t)stream>>>(map_x, map_w, p);
+  lmce_kernel<1><<<(unsigned)grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(map_x, map_w, map_out, p);
   B2_CUDA_CHECK(cudaGetLastError());
   return B2_OK;
 }

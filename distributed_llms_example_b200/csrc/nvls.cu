@@ -586,7 +586,7 @@ extern "C" int b2_allreduce_nvls_inplace(b2_comm* c, uint64_t offset_bytes, int6
   const void* fn = c->world == 2 ? (const void*)allreduce_nvls_inplace_kernel<2>
                  : c->world == 4 ? (const void*)allreduce_nvls_inplace_kernel<4>
                                  : (const void*)allreduce_nvls_inplace_kernel<8>;
-  const int nb = pick_blocks(numel / 4 / c->world, c->max_blocks);
+  const int nb = pick_blocks(numel / 4 / c->world, c->max_blocks, c->ppt);
   long long n_arg = numel;
   float scale_arg = scale;
   int unroll = c->unroll;

@@ -42,42 +42,58 @@ def _workspace(device: torch.device, stream: int, nbytes: int) -> torch.Tensor:
 class _FusedLMHeadCE(torch.autograd.Function):
     @staticmethod
     def forward(ctx, hidden: torch.Tensor, weight: torch.Tensor, target: torch.Tensor, ignore_index: int,
-                round_bf16: bool):
+                round_bf16: bool, keep_logits: bool):
         lib = _lib.load()
         n, d = hidden.shape
         v = weight.shape[0]
         hb = hidden.detach().to(torch.bfloat16).contiguous()
         wb = weight.detach().to(torch.bfloat16).contiguous()
+        ld = (v + 7) // 8 * 8
         with torch.cuda.device(hidden.device):
             stream = torch.cuda.current_stream().cuda_stream
             row_lse = torch.empty(n, dtype=torch.float32, device=hidden.device)
             loss = torch.empty((), dtype=torch.float32, device=hidden.device)
             nvalid = torch.empty(1, dtype=torch.float32, device=hidden.device)
+            logits = torch.empty((n, ld), dtype=torch.bfloat16, device=hidden.device) if keep_logits else None
             need = lib.b2_lmce_workspace_bytes(n, v)
             ws = _workspace(hidden.device, stream, need)
             _lib.check(lib.b2_lmce_forward(hb.data_ptr(), wb.data_ptr(), target.data_ptr(), n, v, d, ignore_index,
                                            1 if round_bf16 else 0, row_lse.data_ptr(), loss.data_ptr(),
-                                           nvalid.data_ptr(), ws.data_ptr(), ws.numel(), stream))
+                                           nvalid.data_ptr(), logits.data_ptr() if keep_logits else None, ld,
+                                           ws.data_ptr(), ws.numel(), stream))
             _lib.count_launch(2)
-        ctx.save_for_backward(hb, wb, target, row_lse, nvalid)
-        ctx.ignore_index, ctx.round_bf16 = ignore_index, round_bf16
+        if keep_logits:
+            ctx.save_for_backward(hb, wb, target, row_lse, nvalid, logits)
+        else:
+            ctx.save_for_backward(hb, wb, target, row_lse, nvalid)
+        ctx.ignore_index, ctx.round_bf16, ctx.keep_logits = ignore_index, round_bf16, keep_logits
         ctx.hidden_dtype, ctx.weight_dtype = hidden.dtype, weight.dtype
         return loss
 
     @staticmethod
     def backward(ctx, grad_output: torch.Tensor):
-        hb, wb, target, row_lse, nvalid = ctx.saved_tensors
+        hb, wb, target, row_lse, nvalid = ctx.saved_tensors[:5]
         lib = _lib.load()
         n, d = hb.shape
         v = wb.shape[0]
         ld = (v + 7) // 8 * 8
         with torch.cuda.device(hb.device):
+            stream = torch.cuda.current_stream().cuda_stream
             g = grad_output.to(torch.float32).contiguous()
             dlogits = torch.empty((n, ld), dtype=torch.bfloat16, device=hb.device)
-            _lib.check(lib.b2_lmce_backward_dlogits(hb.data_ptr(), wb.data_ptr(), target.data_ptr(), row_lse.data_ptr(),
-                                                    g.data_ptr(), nvalid.data_ptr(), n, v, d, ctx.ignore_index,
-                                                    1 if ctx.round_bf16 else 0, dlogits.data_ptr(), ld,
-                                                    torch.cuda.current_stream().cuda_stream))
+            if ctx.keep_logits:
+                # the forward wrote the bf16 logits on their way out of tensor memory: the backward is
+                # the HBM-bound masked-CE kernel on that buffer (one read, one write)
+                logits = ctx.saved_tensors[5]
+                _lib.check(lib.b2_ce_backward(logits.data_ptr(), target.data_ptr(), row_lse.data_ptr(), g.data_ptr(),
+                                              nvalid.data_ptr(), n, v, ld, ctx.ignore_index, _lib.B2_BF16,
+                                              dlogits.data_ptr(), stream))
+            else:
+                # nothing was kept: recompute the logits tile by tile on the tensor cores
+                _lib.check(lib.b2_lmce_backward_dlogits(hb.data_ptr(), wb.data_ptr(), target.data_ptr(),
+                                                        row_lse.data_ptr(), g.data_ptr(), nvalid.data_ptr(), n, v, d,
+                                                        ctx.ignore_index, 1 if ctx.round_bf16 else 0,
+                                                        dlogits.data_ptr(), ld, stream))
             _lib.count_launch()
             dl = dlogits[:, :v]
             d_hidden = d_weight = None
@@ -85,13 +101,22 @@ class _FusedLMHeadCE(torch.autograd.Function):
                 d_hidden = (dl @ wb).to(ctx.hidden_dtype)          # [N, V] x [V, D], library GEMM
             if ctx.needs_input_grad[1]:
                 d_weight = (dl.t() @ hb).to(ctx.weight_dtype)      # [V, N] x [N, D], library GEMM
-        return d_hidden, d_weight, None, None, None
+        return d_hidden, d_weight, None, None, None, None
 
 
 def fused_lm_head_ce(hidden: torch.Tensor, weight: torch.Tensor, target: torch.Tensor, ignore_index: int = -100,
-                     round_bf16: bool = True) -> torch.Tensor:
+                     round_bf16: bool = True, keep_logits: Optional[bool] = None) -> torch.Tensor:
     """``F.cross_entropy(F.linear(hidden, weight).view(-1, V), target.view(-1), ignore_index=...)`` with bf16
-    tensor-core math and fp32 accumulation; ``hidden`` [..., D], ``weight`` [V, D], ``target`` [...]."""
+    tensor-core math and fp32 accumulation; ``hidden`` [..., D], ``weight`` [V, D], ``target`` [...].
+
+    ``keep_logits=True`` (default, ``B2_LMCE_KEEP_LOGITS=0`` flips it): the forward also writes the bf16
+    logits once (it never reads them) and the backward is the HBM-bound masked-CE kernel - the fastest
+    pairing on B200. ``keep_logits=False``: no [N, V] tensor lives between forward and backward; the
+    backward recomputes the logits on the tensor cores (N*V*2 bytes less memory, ~1.4x the time)."""
+    if keep_logits is None:
+        import os
+
+        keep_logits = os.environ.get("B2_LMCE_KEEP_LOGITS", "1") != "0"
     if not hidden.is_cuda or not weight.is_cuda:
         raise RuntimeError("fused_lm_head_ce has no CPU path")
     if weight.dim() != 2 or hidden.shape[-1] != weight.shape[1]:
@@ -102,7 +127,10 @@ def fused_lm_head_ce(hidden: torch.Tensor, weight: torch.Tensor, target: torch.T
     t1 = target.reshape(-1)
     if t1.shape[0] != h2.shape[0] or t1.dtype != torch.int64:
         raise ValueError("target must be int64 with one entry per row of hidden")
-    return _FusedLMHeadCE.apply(h2, weight, t1.contiguous(), int(ignore_index), bool(round_bf16))
+    if keep_logits and not round_bf16:
+        raise ValueError("keep_logits=True stores bf16 logits, so the loss must be taken on bf16 logits too "
+                         "(round_bf16=True)")
+    return _FusedLMHeadCE.apply(h2, weight, t1.contiguous(), int(ignore_index), bool(round_bf16), bool(keep_logits))
 
 
 # ---- lazy logits: how the fused path reaches T5's unmodified forward ---------------------------
@@ -178,9 +206,11 @@ def install_lazy_lm_head(linear: torch.nn.Linear) -> None:
 
     def forward(x: torch.Tensor) -> torch.Tensor:
         if getattr(_tls, "active", False) and x.is_cuda and linear.weight.shape[1] % 64 == 0:
-            if torch.is_autocast_enabled("cuda"):
-                x = x.to(torch.get_autocast_dtype("cuda"))  # what F.linear would compute in
-            return LazyLogits(x, linear.weight)
+            # only where the unfused matmul would run in bf16 anyway (bf16 autocast, or a bf16 model):
+            # an fp32 model keeps its fp32 lm_head, this path never lowers precision by itself
+            autocast_bf16 = torch.is_autocast_enabled("cuda") and torch.get_autocast_dtype("cuda") == torch.bfloat16
+            if autocast_bf16 or (x.dtype == torch.bfloat16 and linear.weight.dtype == torch.bfloat16):
+                return LazyLogits(x.to(torch.bfloat16), linear.weight)
         return cls_forward(linear, x)
 
     linear.forward = forward

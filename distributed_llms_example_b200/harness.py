@@ -53,7 +53,8 @@ class StepConfig:
     max_grad_norm: float = 1.0          # trainer semantics only
     fused_adamw: Optional[bool] = None  # stock impl: torch's fused kernel (what Trainer selects)
     wire: str = "fp32"                  # b200 impl: dtype on NVLink
-    bucket_cap_mb: Optional[float] = None  # DDP bucket size; None = torch's default (25 MiB)
+    bucket_cap_mb: Optional[float] = None  # DDP bucket size; None = the plug-in's / torch's default
+    fused_lm_head: Optional[bool] = None   # b200 impl: lm_head + CE as one tcgen05 kernel (None: B2_FUSED_LM_HEAD)
 
 
 def _no_decay(name: str) -> bool:
@@ -72,7 +73,8 @@ class StepHarness:
                 raise RuntimeError("impl='b200' has no CPU path")
             # the same attach path an unmodified script gets from launch.py: CrossEntropyLoss,
             # torch.optim.AdamW, clip_grad_norm_ and DistributedDataParallel.__init__ are rebound
-            patch.apply(comm_kwargs={"wire": cfg.wire})
+            patch.remove()
+            patch.apply(comm_kwargs={"wire": cfg.wire}, fused_lm_head=cfg.fused_lm_head)
         elif cfg.impl == "stock":
             patch.remove()
         else:

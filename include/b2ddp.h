@@ -115,15 +115,23 @@ int b2_ce_backward(const void* logits, const int64_t* labels, const float* row_l
  *   round_bf16 != 0: each logit is rounded to bf16 before the softmax - bit-for-bit what the
  *          unfused path computes from its bf16 logits tensor; 0 keeps the fp32 accumulator.
  * Outputs as b2_ce_forward: row_lse[n_rows], loss_out[1] (NaN when no row is valid),
- * nvalid_out[1]. workspace: b2_lmce_workspace_bytes(n_rows, vocab) bytes, 16-byte aligned, its
- * first 16 bytes zero before the first call (the kernel leaves them zero). Deterministic.
+ * nvalid_out[1]. logits_out: NULL, or a bf16 [n_rows, logits_stride] buffer (pitch >= vocab,
+ * multiple of 8, base 16-byte aligned; the up to 7 padding columns between vocab and the next
+ * multiple of 8 are written as zeros) that receives the logits once, on their way out of
+ * tensor memory (TMA store from the epilogue) - the forward still never reads them back, and the
+ * backward can then be b2_ce_backward on that buffer, which is the fastest pairing on B200
+ * (re-reading 2 bytes per logit costs less than recomputing 2*d_model flop per logit).
+ * workspace: b2_lmce_workspace_bytes(n_rows, vocab) bytes, 16-byte aligned, its first 16 bytes
+ * zero before the first call (the kernel leaves them zero). Deterministic.
  * ------------------------------------------------------------------------- */
 size_t b2_lmce_workspace_bytes(int64_t n_rows, int64_t vocab);
 int b2_lmce_forward(const void* hidden, const void* weight, const int64_t* labels, int64_t n_rows,
                     int64_t vocab, int64_t d_model, int64_t ignore_index, int round_bf16,
-                    float* row_lse, float* loss_out, float* nvalid_out, void* workspace,
-                    size_t workspace_bytes, b2_stream_t stream);
-/* Backward of the same pair (loss.backward() at train-accelerator.py:222 / train-task.py:292): the
+                    float* row_lse, float* loss_out, float* nvalid_out, void* logits_out,
+                    int64_t logits_stride, void* workspace, size_t workspace_bytes,
+                    b2_stream_t stream);
+/* Memory-lean backward of the same pair (loss.backward() at train-accelerator.py:222 /
+ * train-task.py:292) for a forward that kept no logits: the
  * logits tile is recomputed by the same tcgen05 main loop and the epilogue writes
  *   dlogits[i, j] = (exp(z_ij - lse_i) - [j == y_i]) * grad_out / n_valid      (0 on ignored rows)
  * in bf16 with row pitch `row_stride` elements (>= vocab, multiple of 8). The caller forms
@@ -296,6 +304,11 @@ int b2_allreduce_nvls_inplace(b2_comm* c, uint64_t offset_bytes, int64_t numel, 
  * callers that poll from their own C++ (csrc_torch/ddp_hook.cpp). */
 int b2_comm_status(b2_comm* c);
 int b2_comm_poll(b2_comm* c);
+/* Launch shape of the zero-copy all-reduce kernels (defaults from B2_AR_BLOCKS,
+ * B2_AR_PACKS_PER_THREAD, B2_AR_UNROLL): at most max_blocks CTAs (<= 128), one more CTA per
+ * packs_per_thread 16-byte packs per thread, unroll 0 = tuned default / 1 = more / 2 = fewer
+ * loads in flight per thread. Negative = leave unchanged. Same call on every rank. */
+int b2_comm_tune(b2_comm* c, int max_blocks, int packs_per_thread, int unroll);
 const void* b2_comm_status_word(b2_comm* c);
 /* Sum of squares folded into the all-reduce: replaces the separate read of
  * every gradient that torch.nn.utils.clip_grad_norm_ makes between sync and step in HF Trainer

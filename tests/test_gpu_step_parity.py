@@ -53,3 +53,28 @@ def test_step_losses_match_cpu_reference_and_stock_cuda(golden, name):
     update = (p_stock - init).double().norm()
     assert float((p_ours - p_stock).double().norm() / update) < 2e-2
     assert float(((p_ours - p_stock).abs() > 2e-5).double().mean()) < 1e-4
+
+
+def test_bf16_step_with_fused_lm_head_matches_unfused_plugins():
+    """bf16 autocast, t5-small, Trainer semantics: the step harness with lm_head + CE as ONE tcgen05
+    kernel (patch.apply(fused_lm_head=True): lazy logits, fused.py) against the same harness with the
+    separate CE kernel. Same bf16 logits up to rounding-boundary cases, so the loss trajectories agree
+    to 2e-4 over 4 optimizer steps, and the fused kernels must really have run."""
+    from distributed_llms_example_b200 import _lib, patch
+    from distributed_llms_example_b200.harness import StepConfig, StepHarness
+
+    out = {}
+    try:
+        for fused in (False, True):
+            h = StepHarness(StepConfig(model="t5-small", semantics="trainer", impl="b200", device="cuda:0", batch_size=4,
+                                       grad_accum=1, label_mode="MASK", bf16=True, dropout=0.0, total_steps=20,
+                                       fused_lm_head=fused))
+            batches = h.host_batches(STEPS)
+            before = _lib.launches
+            out[fused] = (np.array([float(h.step([b])) for b in batches]), _lib.launches - before)
+            h.close()
+    finally:
+        patch.remove()
+    np.testing.assert_allclose(out[True][0], out[False][0], rtol=2e-4)
+    # per step: unfused = CE fwd + CE bwd + clip + AdamW = 4 launches; fused = (fwd + finish) + bwd + clip + AdamW = 5
+    assert out[True][1] == STEPS * 5 and out[False][1] == STEPS * 4, (out[True][1], out[False][1])
