@@ -616,3 +616,20 @@ def test_cpp_comm_hook_attaches_and_delegates_to_python_hook():
     for rank, ok, err in outs:
         assert err is None, f"rank {rank}:\n{err}"
         assert ok
+
+
+def test_config1_full_sequence_lengths_match_committed_golden_losses():
+    """BASELINE.json configs[0] at the lengths it names (512-token sources, 128-token targets): t5-small,
+    world size 2 over gloo on CPU, Trainer semantics with gradient accumulation 2, 3 optimizer steps.
+    The per-rank loss trajectories must equal the ones committed in tests/golden/config1_t5small.npz
+    (oracle/make_golden_config1.py, stock torch ops in the build container) to 1e-4 relative - CPU
+    reductions may be blocked differently on another host - and the replicas must stay bit-identical."""
+    from oracle import make_golden_config1 as G
+
+    gold = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "config1_t5small.npz"))
+    outs = G.run(threads=2)
+    for rank, losses, same, checksum, err in outs:
+        assert err is None, f"rank {rank}:\n{err}"
+        assert same, "replicas diverged"
+        np.testing.assert_allclose(losses, gold[f"rank{rank}"], rtol=1e-4)
+    assert outs[0][1] != outs[1][1]  # each rank trains on its own shard (seed 1234 + rank)
