@@ -75,6 +75,8 @@ def parse_args():
     ap.add_argument("--no-stock", action="store_true", help="skip the stock-GPU leg (vs_baseline stays null)")
     ap.add_argument("--no-parity", action="store_true", help="skip the N>1 parity block and the loss comparison")
     ap.add_argument("--dropout", type=float, default=0.1)
+    ap.add_argument("--cuda-graph", type=int, default=None, choices=[0, 1],
+                    help="b200 arm: replay forward + backward from CUDA graphs (default: B2_CUDA_GRAPH)")
     ap.add_argument("--fused-lm-head", type=int, default=None, choices=[0, 1],
                     help="b200 arm: lm_head + CE as one tcgen05 kernel (default: B2_FUSED_LM_HEAD)")
     return ap.parse_args()
@@ -420,7 +422,8 @@ def loss_parity(args, local_rank: int, steps: int = 4) -> dict:
         cfg = StepConfig(model=args.model, semantics=args.semantics, impl=impl, device=f"cuda:{local_rank}",
                          batch_size=args.batch_size, grad_accum=args.grad_accum, label_mode=args.label_mode,
                          bf16=True, dropout=0.0, wire="fp32", bucket_cap_mb=args.bucket_cap_mb, total_steps=1000,
-                         fused_lm_head=None if args.fused_lm_head is None else bool(args.fused_lm_head))
+                         fused_lm_head=None if args.fused_lm_head is None else bool(args.fused_lm_head),
+                         cuda_graph=None if args.cuda_graph is None else bool(args.cuda_graph))
         h = StepHarness(cfg)
         host = h.host_batches(steps * args.grad_accum, seed=4321)
         if impl == "stock":
@@ -476,7 +479,8 @@ def run_gpu_arm(args, impl: str, world: int, local_rank: int, K: int, W: int, wi
                      batch_size=args.batch_size, grad_accum=args.grad_accum, label_mode=args.label_mode,
                      bf16=True, wire=args.wire, bucket_cap_mb=args.bucket_cap_mb, dropout=args.dropout,
                      total_steps=max(1000, 4 * (K + W)),
-                     fused_lm_head=None if args.fused_lm_head is None else bool(args.fused_lm_head))
+                     fused_lm_head=None if args.fused_lm_head is None else bool(args.fused_lm_head),
+                     cuda_graph=None if args.cuda_graph is None else bool(args.cuda_graph))
     h = StepHarness(cfg)
     ga = args.grad_accum
     host = h.host_batches((2 * K + W) * ga)
@@ -598,6 +602,8 @@ def main():
         from distributed_llms_example_b200 import patch as _patch
 
         out["fused_lm_head_ce"] = "t5_forward" in _patch._saved
+        gf = h.model.__dict__.get("_b200_graphed")
+        out["cuda_graph"] = None if gf is None else {"replays": gf.replays, "graphs": len(gf.graphs), "failed": gf.failed}
     failed = False
     if world > 1:
         # optional extras must never cost the headline numbers above

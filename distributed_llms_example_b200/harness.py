@@ -55,6 +55,7 @@ class StepConfig:
     wire: str = "fp32"                  # b200 impl: dtype on NVLink
     bucket_cap_mb: Optional[float] = None  # DDP bucket size; None = the plug-in's / torch's default
     fused_lm_head: Optional[bool] = None   # b200 impl: lm_head + CE as one tcgen05 kernel (None: B2_FUSED_LM_HEAD)
+    cuda_graph: Optional[bool] = None      # b200 impl: replay forward + backward from CUDA graphs (None: B2_CUDA_GRAPH)
 
 
 def _no_decay(name: str) -> bool:
@@ -74,7 +75,7 @@ class StepHarness:
             # the same attach path an unmodified script gets from launch.py: CrossEntropyLoss,
             # torch.optim.AdamW, clip_grad_norm_ and DistributedDataParallel.__init__ are rebound
             patch.remove()
-            patch.apply(comm_kwargs={"wire": cfg.wire}, fused_lm_head=cfg.fused_lm_head)
+            patch.apply(comm_kwargs={"wire": cfg.wire}, fused_lm_head=cfg.fused_lm_head, cuda_graph=cfg.cuda_graph)
         elif cfg.impl == "stock":
             patch.remove()
         else:

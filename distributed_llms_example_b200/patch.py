@@ -91,7 +91,19 @@ def patch_ddp(**comm_kwargs) -> None:
                 kwargs["bucket_cap_mb"] = cap
             if "gradient_as_bucket_view" not in kwargs and os.environ.get("B2_DDP_BUCKET_VIEW", "1") != "0":
                 kwargs["gradient_as_bucket_view"] = True
-        orig(self, module, *args, **kwargs)
+        if ours and "cuda_graph" in _saved:
+            # DDP creates (and keeps alive) every parameter's AccumulateGrad node here, and a node remembers
+            # the stream that was current at its creation. Created on the legacy default stream they make
+            # any later CUDA-graph capture of the backward illegal ("would make the legacy stream depend on a
+            # capturing stream"), so with graph replay on, DDP is constructed on a side stream - the
+            # arrangement torch's own CUDA-graph + DDP recipe prescribes.
+            side = torch.cuda.Stream(device=next(module.parameters()).device)
+            side.wait_stream(torch.cuda.current_stream(side.device))
+            with torch.cuda.stream(side):
+                orig(self, module, *args, **kwargs)
+            torch.cuda.current_stream(side.device).wait_stream(side)
+        else:
+            orig(self, module, *args, **kwargs)
         if ours:
             from . import comm
 
@@ -152,10 +164,23 @@ def patch_fused_lm_head() -> None:
     t5.T5ForConditionalGeneration.forward = forward
 
 
+def patch_cuda_graph() -> None:
+    """Opt-in (``B2_CUDA_GRAPH=1`` or ``apply(cuda_graph=True)``): the model's forward + backward are
+    captured in CUDA graphs once the batch shapes repeat and replayed from then on (graphs.py). Applied
+    after ``patch_fused_lm_head`` so that the captured forward already contains the fused kernel."""
+    from . import graphs
+
+    graphs.install()
+    _saved.setdefault("cuda_graph", True)
+
+
 def apply(cross_entropy: bool = True, adamw: bool = True, ddp: bool = True, fold_clip: bool = True,
-          comm_kwargs: dict | None = None, fused_lm_head: bool | None = None) -> None:
+          comm_kwargs: dict | None = None, fused_lm_head: bool | None = None,
+          cuda_graph: bool | None = None) -> None:
     if fused_lm_head is None:
         fused_lm_head = os.environ.get("B2_FUSED_LM_HEAD", "0") == "1"
+    if cuda_graph is None:
+        cuda_graph = os.environ.get("B2_CUDA_GRAPH", "0") == "1"
     if cross_entropy:
         patch_cross_entropy()
     if fused_lm_head and cross_entropy:
@@ -166,12 +191,18 @@ def apply(cross_entropy: bool = True, adamw: bool = True, ddp: bool = True, fold
         patch_ddp(**(comm_kwargs or {}))
     if fold_clip:
         patch_clip_grad_norm()
+    if cuda_graph:
+        patch_cuda_graph()
 
 
 def remove() -> None:
     """Undo apply() (used by the benchmark to time the stock path in the same process)."""
     from torch.nn.parallel import DistributedDataParallel as DDP
 
+    if _saved.pop("cuda_graph", None):  # outermost wrapper of T5's forward: comes off first
+        from . import graphs
+
+        graphs.uninstall()
     for key, val in list(_saved.items()):
         if key.startswith("ce:"):
             importlib.import_module(key[3:]).CrossEntropyLoss = val
