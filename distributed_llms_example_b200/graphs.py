@@ -12,7 +12,7 @@ captured once and replayed.
 
 How it attaches: ``T5ForConditionalGeneration.forward`` still runs as written, but only while it is
 being captured. ``patch.patch_cuda_graph()`` wraps it; a training call with labels on a CUDA model first
-runs eagerly ``B2_GRAPH_EAGER_STEPS`` (3) times per shape signature, then
+runs eagerly ``B2_GRAPH_EAGER_STEPS`` (2) times per shape signature, then
 ``torch.cuda.make_graphed_callables`` captures forward and backward (this package's CE / fused lm_head
 kernels included - they are ordinary stream-ordered launches), and later calls with the same signature
 replay. The returned object is a ``Seq2SeqLMOutput`` holding the loss only; anything that needs logits,
@@ -81,7 +81,11 @@ class GraphedForward:
 
     def __init__(self, model, orig_forward):
         self.model, self.orig = model, orig_forward
-        self.eager_steps = int(os.environ.get("B2_GRAPH_EAGER_STEPS", "3"))
+        self.eager_steps = int(os.environ.get("B2_GRAPH_EAGER_STEPS", "2"))
+        # every captured signature keeps its own activations alive (~25 GB for flan-t5-large at batch 8):
+        # ragged batches (collator padding to the longest) would multiply that, so only the first few
+        # signatures are captured and the rest stay eager
+        self.max_graphs = int(os.environ.get("B2_GRAPH_MAX", "2"))
         self.seen: dict[tuple, int] = {}
         self.graphs: dict[tuple, Any] = {}
         self.failed: Optional[str] = None
@@ -110,7 +114,7 @@ class GraphedForward:
         if g is None:
             n = self.seen.get(sig, 0)
             self.seen[sig] = n + 1
-            if n < self.eager_steps:
+            if n < self.eager_steps or len(self.graphs) >= self.max_graphs:
                 return self.orig(self.model, **kwargs)
             g = self._capture(sig, kwargs)
             if g is None:

@@ -78,3 +78,31 @@ def test_bf16_step_with_fused_lm_head_matches_unfused_plugins():
     np.testing.assert_allclose(out[True][0], out[False][0], rtol=2e-4)
     # per step: unfused = CE fwd + CE bwd + clip + AdamW = 4 launches; fused = (fwd + finish) + bwd + clip + AdamW = 5
     assert out[True][1] == STEPS * 5 and out[False][1] == STEPS * 4, (out[True][1], out[False][1])
+
+
+def test_cuda_graph_replay_is_bit_identical_to_eager_launches():
+    """graphs.py: after 3 eager steps the model's forward + backward are captured and replayed. Same
+    kernels, same order, same inputs: with dropout 0 the loss trajectory must equal the eager run's bit
+    for bit, the replays must really have happened, and this package's kernels inside the graph are
+    counted per replay."""
+    from distributed_llms_example_b200 import _lib, patch
+    from distributed_llms_example_b200.harness import StepConfig, StepHarness
+
+    out = {}
+    steps = 8
+    try:
+        for graph in (False, True):
+            h = StepHarness(StepConfig(model="t5-small", semantics="trainer", impl="b200", device="cuda:0", batch_size=4,
+                                       grad_accum=1, label_mode="REF", bf16=True, dropout=0.0, total_steps=20,
+                                       fused_lm_head=True, cuda_graph=graph))
+            batches = h.host_batches(steps)
+            before = _lib.launches
+            losses = [float(h.step([b])) for b in batches]
+            gf = h.model.__dict__.get("_b200_graphed")
+            out[graph] = (losses, _lib.launches - before, None if gf is None else (gf.replays, len(gf.graphs), gf.kernels_per_replay))
+            h.close()
+    finally:
+        patch.remove()
+    assert out[True][0] == out[False][0]
+    assert out[False][2] is None and out[True][2] == (steps - 2, 1, 3)   # fused fwd + finish + CE backward
+    assert out[True][1] == out[False][1] + (3 + 1) * 3                    # + the capture's own warm-up launches
