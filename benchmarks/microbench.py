@@ -472,7 +472,7 @@ def bench_allreduce_tune(args):
                 off = comm.nvls_offset(xp)
                 paths.append(("nvls_inplace", lambda: comm.allreduce_nvls_inplace_(off, n, 1.0 / world)))
             iters = max(5, min(args.iters, int(1500 / max(mb, 1))))
-            shapes = [(b, p, u) for b in (48, 96, 128) for p in (2, 4, 8) for u in (0, 1, 2)] if not sumsq else [(-1, -1, -1)]
+            shapes = [(b, p, u) for b in (48, 96, 128) for p in (2, 4, 8) for u in (0, 1, 2)]  # u: push 0/1/2 = tuned/more/fewer; NVLS (since the r2 sweep) 0|2 = 2, 1 = 8, 3 = 4 loads if not sumsq else [(-1, -1, -1)]
             for path, fn in paths:
                 for (blocks, ppt, unroll) in shapes:
                     if blocks > 0:

@@ -459,10 +459,12 @@ allreduce_nvls_inplace_kernel(const __grid_constant__ NvlsArgs a, long long nume
   if (!gated && !cross_barrier<W>(v, epoch, timeout_ns)) { poison_local(v, numel); return; }
   const long long slo = min((long long)rank * Q, npack), shi = min(slo + Q, npack);
   const long long lo = min(slo + (long long)b * q, shi), hi = min(lo + q, shi);
-  // B2_AR_UNROLL: 0 = 4 (default), 1 = 8, 2 = 2 switch reads in flight per thread
+  // switch reads in flight per thread: 2 by default - at world 8 the in-switch reduction is the
+  // bottleneck and deeper queues only add contention (sweep in profiles/r2_allreduce_tune_w8.jsonl:
+  // 128 MiB 319 us with 2, 336 us with 4, 357 us with 8); B2_AR_UNROLL = 1 -> 8, 3 -> 4
   if (unroll == 1) nvls_range<8>(a.mc, lo, hi, scale, sq);
-  else if (unroll == 2) nvls_range<2>(a.mc, lo, hi, scale, sq);
-  else nvls_range<4>(a.mc, lo, hi, scale, sq);
+  else if (unroll == 3) nvls_range<4>(a.mc, lo, hi, scale, sq);
+  else nvls_range<2>(a.mc, lo, hi, scale, sq);
   if (rank == 0 && b == 0 && tid < numel - tail0) {
     char* p = a.mc + tail0 * 4 + (size_t)tid * 4;
     const float t = __fmul_rn(multimem_ld_reduce_f32(p), scale);

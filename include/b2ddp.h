@@ -307,7 +307,8 @@ int b2_comm_poll(b2_comm* c);
 /* Launch shape of the zero-copy all-reduce kernels (defaults from B2_AR_BLOCKS,
  * B2_AR_PACKS_PER_THREAD, B2_AR_UNROLL): at most max_blocks CTAs (<= 128), one more CTA per
  * packs_per_thread 16-byte packs per thread, unroll 0 = tuned default / 1 = more / 2 = fewer
- * loads in flight per thread. Negative = leave unchanged. Same call on every rank. */
+ * loads in flight per thread (in-switch kernel: 0 and 2 = 2 loads, 1 = 8, 3 = 4). Negative = leave
+ * unchanged. Same call on every rank. */
 int b2_comm_tune(b2_comm* c, int max_blocks, int packs_per_thread, int unroll);
 const void* b2_comm_status_word(b2_comm* c);
 /* Sum of squares folded into the all-reduce: replaces the separate read of
