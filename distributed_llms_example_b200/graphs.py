@@ -15,7 +15,9 @@ being captured. ``patch.patch_cuda_graph()`` wraps it; a training call with labe
 runs eagerly ``B2_GRAPH_EAGER_STEPS`` (2) times per shape signature, then
 ``torch.cuda.make_graphed_callables`` captures forward and backward (this package's CE / fused lm_head
 kernels included - they are ordinary stream-ordered launches), and later calls with the same signature
-replay. The returned object is a ``Seq2SeqLMOutput`` holding the loss only; anything that needs logits,
+replay. The capture is made in two segments, encoder | decoder + loss (``B2_GRAPH_SEGMENTS``): the decoder's
+gradients then reach DDP before the encoder's backward graph is launched, so their buckets are
+all-reduced while it runs (2 GPUs: 99.8 -> 97.6 ms per step). The returned object is a ``Seq2SeqLMOutput`` holding the loss only; anything that needs logits,
 another shape, eval mode or extra arguments takes the eager path. DDP, the comm hook, AdamW and the clip
 are untouched: gradients leave the graph through autograd's AccumulateGrad like any others.
 
@@ -76,6 +78,29 @@ class _LossOnly(torch.nn.Module):
                           decoder_input_ids=decoder_input_ids).loss
 
 
+class _Encoder(torch.nn.Module):
+    """First segment of the two-segment capture: the encoder stack, exactly as T5's forward calls it."""
+
+    def __init__(self, model):
+        super().__init__()
+        self.encoder = model.encoder
+
+    def forward(self, input_ids, attention_mask):
+        return self.encoder(input_ids=input_ids, attention_mask=attention_mask)[0]
+
+
+class _DecoderLoss(torch.nn.Module):
+    """Second segment: T5's own forward, given the encoder's output (its ``encoder_outputs`` argument)."""
+
+    def __init__(self, model, orig_forward):
+        super().__init__()
+        self.model, self._orig = model, orig_forward
+
+    def forward(self, encoder_hidden, attention_mask, labels, decoder_input_ids):
+        return self._orig(self.model, encoder_outputs=(encoder_hidden,), attention_mask=attention_mask, labels=labels,
+                          decoder_input_ids=decoder_input_ids).loss
+
+
 class GraphedForward:
     """Per-model cache {shape signature -> graphed callable}; see the module docstring."""
 
@@ -86,6 +111,10 @@ class GraphedForward:
         # ragged batches (collator padding to the longest) would multiply that, so only the first few
         # signatures are captured and the rest stay eager
         self.max_graphs = int(os.environ.get("B2_GRAPH_MAX", "2"))
+        # 2 segments (encoder | decoder + loss): the decoder's gradients leave the replayed backward before
+        # the encoder's backward starts, so under DDP their buckets are all-reduced WHILE the encoder's
+        # backward graph runs instead of after the whole backward. 1 = one graph for everything.
+        self.segments = int(os.environ.get("B2_GRAPH_SEGMENTS", "2"))
         self.seen: dict[tuple, int] = {}
         self.graphs: dict[tuple, Any] = {}
         self.failed: Optional[str] = None
@@ -121,7 +150,11 @@ class GraphedForward:
                 return self.orig(self.model, **kwargs)
         ac, acd = sig[-2], sig[-1]
         with torch.autocast("cuda", dtype=acd, enabled=bool(ac), cache_enabled=False):
-            loss = g(*(kwargs[k] for k in _KEYS))
+            if isinstance(g, tuple):
+                hidden = g[0](kwargs["input_ids"], kwargs["attention_mask"])
+                loss = g[1](hidden, kwargs["attention_mask"], kwargs["labels"], kwargs["decoder_input_ids"])
+            else:
+                loss = g(*(kwargs[k] for k in _KEYS))
         self.replays += 1
         _lib_count(self.kernels_per_replay)
         return Seq2SeqLMOutput(loss=loss)
@@ -137,8 +170,18 @@ class GraphedForward:
         torch.cuda.graph = _ThreadLocalGraph  # see _ThreadLocalGraph
         try:
             with torch.autocast("cuda", dtype=acd, enabled=bool(ac), cache_enabled=False):
-                g = torch.cuda.make_graphed_callables(_LossOnly(self.model, self.orig), sample,
-                                                      num_warmup_iters=warmup, allow_unused_input=True)
+                if self.segments >= 2:
+                    enc = _Encoder(self.model)
+                    with torch.no_grad():
+                        probe = enc(sample[0], sample[1])  # shape / dtype of the segment boundary
+                    hidden = torch.zeros_like(probe).requires_grad_(True)
+                    g = torch.cuda.make_graphed_callables(
+                        (enc, _DecoderLoss(self.model, self.orig)),
+                        ((sample[0], sample[1]), (hidden, sample[1], sample[2], sample[3])),
+                        num_warmup_iters=warmup, allow_unused_input=True)
+                else:
+                    g = torch.cuda.make_graphed_callables(_LossOnly(self.model, self.orig), sample,
+                                                          num_warmup_iters=warmup, allow_unused_input=True)
         except Exception as exc:
             # A capture that dies half way leaves torch's CUDA generator registered with a dead graph;
             # there is no clean way back to the eager path, so say so instead of training on.
