@@ -129,6 +129,13 @@ def bench_ce(args):
 
             fmed, _ = time_ms(ours_fwd, args.iters, args.warmup, flush)
             bmed, _ = time_ms(ours_bwd, args.iters, args.warmup, flush)
+            sweep = {}
+            if args.ce_sweep and tdt is torch.bfloat16:
+                for sp in (1, 2, 4, 8):
+                    for cap in (0, 4):
+                        os.environ["B2_CE_SPLIT"], os.environ["B2_CE_FWD_CTAS_PER_SM"] = str(sp), str(cap)
+                        sweep[f"split{sp}_cap{cap}"] = round(run(fwd) * 1e3, 1)
+                os.environ.pop("B2_CE_SPLIT"); os.environ.pop("B2_CE_FWD_CTAS_PER_SM")
             fb, bb = n * v * s, n * v * s * (1 + frac_valid)  # backward reads only the valid rows
             emit(bench="ce", dtype=str(tdt).split(".")[-1], rows=n, impl="b200", l2_flush=flush, fwd_ms=fmed,
                  bwd_ms=bmed, fwd_gbs=fb / fmed / 1e6, bwd_gbs=bb / bmed / 1e6,
@@ -217,11 +224,18 @@ def bench_ce_kernel(args):
                 os.environ["B2_CE_POLY"] = "1" if os.environ.get("B2_CE_POLY") != "1" else "0"
                 poly_ms = run(fwd)
                 os.environ["B2_CE_POLY"] = "1" if os.environ.get("B2_CE_POLY") != "1" else "0"
+            sweep = {}
+            if args.ce_sweep and tdt is torch.bfloat16:
+                for sp in (1, 2, 4, 8):
+                    for cap in (0, 4):
+                        os.environ["B2_CE_SPLIT"], os.environ["B2_CE_FWD_CTAS_PER_SM"] = str(sp), str(cap)
+                        sweep[f"split{sp}_cap{cap}"] = round(run(fwd) * 1e3, 1)
+                os.environ.pop("B2_CE_SPLIT"); os.environ.pop("B2_CE_FWD_CTAS_PER_SM")
             fb, bb = n * v * s, n * v * s * (1 + frac_valid)
             emit(bench="ce_kernel", dtype=str(tdt).split(".")[-1], rows=n, buffers=nbuf, reps=reps,
                  fwd_us=f_ms * 1e3, bwd_us=b_ms * 1e3, fwd_gbs=fb / f_ms / 1e6, bwd_gbs=bb / b_ms / 1e6,
                  fwd_frac_measured_peak=fb / f_ms / 1e6 / PEAK, bwd_frac_measured_peak=bb / b_ms / 1e6 / PEAK,
-                 fwd_us_other_exp_mode=None if poly_ms is None else poly_ms * 1e3,
+                 fwd_us_other_exp_mode=None if poly_ms is None else poly_ms * 1e3, fwd_us_sweep=sweep,
                  env={k: os.environ[k] for k in os.environ if k.startswith("B2_CE")})
             del zs, ds
             torch.cuda.empty_cache()
@@ -498,6 +512,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("bench", choices=["adamw", "ce", "ce_kernel", "lmce", "allreduce", "allreduce_emulated", "allreduce_tune"])
     ap.add_argument("--d-model", type=int, default=1024)
+    ap.add_argument("--ce-sweep", action="store_true", help="ce_kernel: sweep row split x grid cap for the bf16 forward")
     ap.add_argument("--models", nargs="+", default=["t5-small", "flan-t5-base", "flan-t5-large", "flan-t5-xl"])
     ap.add_argument("--rows", nargs="+", type=int, default=[128, 1024, 8192, 32768])
     ap.add_argument("--sizes-mb", nargs="+", type=float, default=[1, 2, 4, 8, 16, 25, 32, 64, 128, 256, 512, 1024])

@@ -467,7 +467,7 @@ static int env_int(const char* name, int dflt) {
   return (v && *v) ? std::atoi(v) : dflt;
 }
 static long long fwd_grid(long long items) {  // items are per-warp work units, 8 warps per CTA
-  static const int cap = env_int("B2_CE_FWD_CTAS_PER_SM", 0);
+  const int cap = env_int("B2_CE_FWD_CTAS_PER_SM", 0);  // read per call: benchmarks sweep it in one process
   const long long ctas = (items + kCeWarps - 1) / kCeWarps;
   return cap > 0 ? std::min<long long>(ctas, (long long)kNumSMs * cap) : ctas;
 }
@@ -477,12 +477,15 @@ static long long bwd_grid(long long items) {
 }
 
 static int pick_split(long long n_rows) {
-  // A row is split over several warps only while one warp per row cannot fill the chip twice
-  // over (148 SMs x 32 resident warps): small batches are latency-bound, and shorter pieces
-  // mean fewer dependent load rounds per warp.
-  const long long target = 2ll * kNumSMs * kCeFwdCtasPerSM * kCeWarps;
+  // A row is split over several warps only while there are fewer rows than ~2048 warps' worth of
+  // work: measured on B200 (profiles/README.md, round 2 sweep), one warp per row wins from 2048 rows
+  // up - split rows pay for the partials and the last CTA's fold (N = 8192: 100.8 us unsplit, 122.2 us
+  // split in 2; N = 2048: 33.7 vs 47.8 us split in 8) - and 2048 work items is where N = 1024 is
+  // fastest (25.6 us split in 2, 29.7 us unsplit, 30.0 us split in 8).
+  const int forced = env_int("B2_CE_SPLIT", 0);  // tuning override (power of two <= 16)
+  if (forced >= 1 && forced <= kCeMaxSplit && (forced & (forced - 1)) == 0) return forced;
   int s = 1;
-  while (s < kCeMaxSplit && n_rows * s < target) s <<= 1;
+  while (s < kCeMaxSplit && n_rows * s < 2048) s <<= 1;
   return s;
 }
 
