@@ -106,3 +106,30 @@ def test_cuda_graph_replay_is_bit_identical_to_eager_launches():
     assert out[True][0] == out[False][0]
     assert out[False][2] is None and out[True][2] == (steps - 2, 1, 3)   # fused fwd + finish + CE backward
     assert out[True][1] == out[False][1] + (3 + 1) * 3                    # + the capture's own warm-up launches
+
+
+def test_cuda_graph_with_ragged_batches_mixes_replay_and_eager_correctly():
+    """Label mode MASK: the collator pads targets to the longest in the batch (multiple of 8), so batch
+    shapes vary. Only B2_GRAPH_MAX (2) signatures are captured, every other shape stays on the eager
+    path - and the mixture must give exactly the losses of an all-eager run (dropout 0)."""
+    from distributed_llms_example_b200 import patch
+    from distributed_llms_example_b200.harness import StepConfig, StepHarness
+
+    out = {}
+    steps = 16
+    try:
+        for graph in (False, True):
+            h = StepHarness(StepConfig(model="t5-small", semantics="accelerate", impl="b200", device="cuda:0",
+                                       batch_size=2, grad_accum=1, label_mode="MASK", bf16=True, dropout=0.0,
+                                       total_steps=40, fused_lm_head=True, cuda_graph=graph))
+            batches = h.host_batches(steps)
+            batches = batches + batches[:4]          # repeat some shapes so that captures do get replayed
+            losses = [float(h.step([b])) for b in batches]
+            gf = h.model.__dict__.get("_b200_graphed")
+            out[graph] = (losses, None if gf is None else (gf.replays, len(gf.graphs), len(gf.seen)))
+            h.close()
+    finally:
+        patch.remove()
+    assert out[True][0] == out[False][0]
+    replays, graphs, shapes = out[True][1]
+    assert graphs <= 2 and shapes >= graphs
