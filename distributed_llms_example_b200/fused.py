@@ -1,4 +1,4 @@
-"""Fused lm_head + label-masked cross-entropy, opt-in.
+"""Fused lm_head + label-masked cross-entropy; on by default, ``B2_FUSED_LM_HEAD=0`` off.
 
 Reference: T5 computes ``lm_logits = self.lm_head(sequence_output)`` and then
 ``CrossEntropyLoss(ignore_index=-100)(lm_logits.view(-1, V), labels.view(-1))``

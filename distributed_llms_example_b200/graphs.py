@@ -1,5 +1,5 @@
-"""CUDA-graph replay of the model's forward + backward, opt-in (``B2_CUDA_GRAPH=1`` or
-``patch.apply(cuda_graph=True)``).
+"""CUDA-graph replay of the model's forward + backward (on by default; ``B2_CUDA_GRAPH=0`` or
+``patch.apply(cuda_graph=False)`` switches it off).
 
 Why: one flan-t5-large step issues ~9 400 eager kernels; the step is bound by the host issuing them
 (profiles/r1_bench_launch_list_summary.txt), so the kernels of this package cannot move samples/s by

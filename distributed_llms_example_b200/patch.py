@@ -91,7 +91,7 @@ def patch_ddp(**comm_kwargs) -> None:
                 kwargs["bucket_cap_mb"] = cap
             if "gradient_as_bucket_view" not in kwargs and os.environ.get("B2_DDP_BUCKET_VIEW", "1") != "0":
                 kwargs["gradient_as_bucket_view"] = True
-        if ours and "cuda_graph" in _saved:
+        if ours and "cuda_graph" in _saved and next(module.parameters()).is_cuda:
             # DDP creates (and keeps alive) every parameter's AccumulateGrad node here, and a node remembers
             # the stream that was current at its creation. Created on the legacy default stream they make
             # any later CUDA-graph capture of the backward illegal ("would make the legacy stream depend on a
@@ -138,7 +138,7 @@ def patch_clip_grad_norm() -> None:
 
 
 def patch_fused_lm_head() -> None:
-    """Opt-in (``B2_FUSED_LM_HEAD=1`` or ``apply(fused_lm_head=True)``): T5's ``lm_head`` + loss become
+    """On by default (``B2_FUSED_LM_HEAD=0`` or ``apply(fused_lm_head=False)`` switches it off): T5's ``lm_head`` + loss become
     one tcgen05 kernel (fused.py). ``T5ForConditionalGeneration.forward`` runs as written; it is only
     wrapped so that, when called with labels in training mode on a CUDA model, its ``lm_head`` answers
     with lazy logits that the rebound CrossEntropyLoss turns into the fused call. Needs
@@ -165,7 +165,7 @@ def patch_fused_lm_head() -> None:
 
 
 def patch_cuda_graph() -> None:
-    """Opt-in (``B2_CUDA_GRAPH=1`` or ``apply(cuda_graph=True)``): the model's forward + backward are
+    """On by default (``B2_CUDA_GRAPH=0`` or ``apply(cuda_graph=False)`` switches it off): the model's forward + backward are
     captured in CUDA graphs once the batch shapes repeat and replayed from then on (graphs.py). Applied
     after ``patch_fused_lm_head`` so that the captured forward already contains the fused kernel."""
     from . import graphs
@@ -177,10 +177,13 @@ def patch_cuda_graph() -> None:
 def apply(cross_entropy: bool = True, adamw: bool = True, ddp: bool = True, fold_clip: bool = True,
           comm_kwargs: dict | None = None, fused_lm_head: bool | None = None,
           cuda_graph: bool | None = None) -> None:
+    # Both extensions are on unless switched off: an unmodified script run through launch.py gets the
+    # same configuration bench.py measures. Each falls back by itself where it does not apply (no bf16
+    # autocast, another model family, changing batch shapes, extra forward arguments, eval mode).
     if fused_lm_head is None:
-        fused_lm_head = os.environ.get("B2_FUSED_LM_HEAD", "0") == "1"
+        fused_lm_head = os.environ.get("B2_FUSED_LM_HEAD", "1") != "0"
     if cuda_graph is None:
-        cuda_graph = os.environ.get("B2_CUDA_GRAPH", "0") == "1"
+        cuda_graph = os.environ.get("B2_CUDA_GRAPH", "1") != "0"
     if cross_entropy:
         patch_cross_entropy()
     if fused_lm_head and cross_entropy:

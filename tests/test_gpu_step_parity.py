@@ -68,7 +68,7 @@ def test_bf16_step_with_fused_lm_head_matches_unfused_plugins():
         for fused in (False, True):
             h = StepHarness(StepConfig(model="t5-small", semantics="trainer", impl="b200", device="cuda:0", batch_size=4,
                                        grad_accum=1, label_mode="MASK", bf16=True, dropout=0.0, total_steps=20,
-                                       fused_lm_head=fused))
+                                       fused_lm_head=fused, cuda_graph=False))
             batches = h.host_batches(STEPS)
             before = _lib.launches
             out[fused] = (np.array([float(h.step([b])) for b in batches]), _lib.launches - before)
