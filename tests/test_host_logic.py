@@ -633,3 +633,62 @@ def test_config1_full_sequence_lengths_match_committed_golden_losses():
         assert same, "replicas diverged"
         np.testing.assert_allclose(losses, gold[f"rank{rank}"], rtol=1e-4)
     assert outs[0][1] != outs[1][1]  # each rank trains on its own shard (seed 1234 + rank)
+
+
+# ---- round-2 host logic that needs no GPU: lazy logits and the graph-replay front door ---------------
+def test_lazy_logits_stay_lazy_for_t5s_view_and_materialise_for_anything_else():
+    """fused.LazyLogits is what a patched lm_head returns: T5's `lm_logits.view(-1, lm_logits.size(-1))`
+    must keep it lazy (so the rebound CrossEntropyLoss can make the fused call), every other use must see
+    the real `hidden @ weight.T`."""
+    import torch.nn.functional as F
+
+    from distributed_llms_example_b200.fused import LazyLogits, lazy_parts
+
+    torch.manual_seed(0)
+    h, w = torch.randn(2, 5, 64), torch.randn(100, 64)
+    z = LazyLogits(h, w)
+    assert z.shape == (2, 5, 100) and z.size(-1) == 100 and z.device == h.device and z.dtype == h.dtype
+    v = z.view(-1, z.size(-1))
+    assert isinstance(v, LazyLogits) and v.shape == (10, 100)
+    hid, wt = lazy_parts(v)
+    assert hid.shape == (10, 64) and wt is w and lazy_parts(torch.zeros(3)) is None
+    real = h @ w.t()
+    assert torch.equal(z.argmax(-1), real.argmax(-1))                      # materialises on demand
+    assert torch.allclose(z.view(10, 100, 1).squeeze(-1), real.view(10, 100))  # a view that changes the last dim too
+    y = torch.randint(0, 100, (10,))
+    assert torch.allclose(F.cross_entropy(v, y), F.cross_entropy(real.view(10, 100), y))
+
+
+def test_graph_replay_front_door_leaves_cpu_models_and_odd_calls_on_the_eager_path():
+    """patch.apply(cuda_graph=True) wraps T5ForConditionalGeneration.forward. A CPU model, an eval-mode
+    call, a call without labels or with extra arguments must all run T5's own forward unchanged (same
+    loss as unpatched), nothing is captured, and remove() restores both the forward and eager_mask."""
+    from transformers import masking_utils as mu
+    from transformers.models.t5 import modeling_t5 as t5
+
+    from distributed_llms_example_b200 import graphs, patch
+    from distributed_llms_example_b200.synthetic import build_model
+
+    fwd0, mask0 = t5.T5ForConditionalGeneration.forward, mu.AttentionMaskInterface._global_mapping["eager"]
+    m = build_model("t5-small", 0.0).train()
+    b = {"input_ids": torch.randint(2, 100, (2, 16)), "attention_mask": torch.ones(2, 16, dtype=torch.long),
+         "labels": torch.randint(2, 100, (2, 8))}
+    b["decoder_input_ids"] = m._shift_right(b["labels"])
+    ref = float(m(**b).loss.detach())
+    patch.apply(cross_entropy=False, adamw=False, ddp=False, fold_clip=False, cuda_graph=True, fused_lm_head=False)
+    try:
+        assert t5.T5ForConditionalGeneration.forward is not fwd0
+        assert mu.AttentionMaskInterface._global_mapping["eager"] is graphs.capture_safe_eager_mask
+        for _ in range(4):   # more calls than B2_GRAPH_EAGER_STEPS: a CUDA model would be captured by now
+            assert float(m(**b).loss.detach()) == ref   # the capture-safe mask gives the same values
+        assert m.__dict__.get("_b200_graphed") is None   # CPU model: the graph front door was never entered
+        gf = graphs.GraphedForward(m, fwd0)
+        assert gf.signature(b) is None                                     # CPU tensors
+        assert gf.signature({**b, "output_attentions": True}) is None      # extra argument
+        assert gf.signature({k: v for k, v in b.items() if k != "labels"}) is None
+        m.eval()
+        assert gf.signature(b) is None
+    finally:
+        patch.remove()
+    assert t5.T5ForConditionalGeneration.forward is fwd0
+    assert mu.AttentionMaskInterface._global_mapping["eager"] is mask0
